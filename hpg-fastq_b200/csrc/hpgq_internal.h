@@ -1,0 +1,60 @@
+// hpgq_internal.h -- kernel argument block and launcher prototypes shared by the .cu files.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/hpg_fastq_cuda.h"
+
+// Everything a QC kernel needs, passed by value (fits the 4 KB kernel-parameter space easily).
+struct hq_kargs {
+  // batch (device pointers, see hpgq_batch_submit_device for alignment/padding rules)
+  const uint8_t *seq;
+  const uint8_t *qual;
+  const uint32_t *idx;
+  uint32_t n_reads;
+  uint32_t work; // HPGQ_WORK_*
+  // filter thresholds, already mapped to raw-ASCII means (Phred + offset) and clamped
+  int32_t min_len, max_len;
+  int32_t q_lo, q_hi; // inclusive bounds on the mean raw quality byte
+  int32_t max_ooq, max_n;
+  uint32_t c_lo, c_hi; // hq_ooq_const_lo/hi of the same bounds
+  int32_t f_ll, f_lq_lo, f_lq_hi; // filter left window (length, raw-ASCII mean bounds)
+  int32_t f_rl, f_rq_lo, f_rq_hi;
+  int32_t e_ll, e_lq_lo, e_lq_hi; // edit (trim) left window
+  int32_t e_rl, e_rq_lo, e_rq_hi;
+  int32_t phred;
+  int32_t k2, cg_k, cg_base_quality;
+  uint32_t Lcap;
+  // flat counter block and section offsets (u64 words)
+  unsigned long long *ctr;
+  uint32_t o_len_hist, o_sumq, o_qual_hist, o_gc_hist, o_accq, o_A, o_C, o_G, o_T, o_N;
+  uint64_t o_k5, o_k5pos, o_k2, o_cg_seq, o_cg_q;
+  // per-read outputs
+  uint8_t *mask;     // may be NULL
+  hpgq_trim_t *trim; // may be NULL
+  // tiled-kernel geometry
+  uint32_t RT;          // reads per tile (multiple of 4)
+  uint32_t G;           // lanes per read group
+  uint32_t stage_bytes; // capacity of one seq (and one qual) stage buffer
+  uint32_t n_tiles;
+};
+
+// launchers (return cudaGetLastError()); `launches` is incremented per kernel launched
+cudaError_t hq_launch_qc_simple(const hq_kargs &a, cudaStream_t st, uint64_t *launches);
+// returns cudaErrorInvalidValue if the batch does not fit the tiled kernel (max read length > 640)
+cudaError_t hq_launch_qc_tiled(hq_kargs a, uint32_t max_len_in_batch, int sm_count, cudaStream_t st,
+                               uint64_t *launches);
+bool hq_tiled_supports(uint32_t max_len_in_batch, uint32_t work);
+cudaError_t hq_launch_kmers_cg(const hq_kargs &a, cudaStream_t st, uint64_t *launches);
+cudaError_t hq_launch_maxlen(const uint32_t *idx, uint32_t n, uint32_t *d_out, cudaStream_t st, uint64_t *launches);
+
+struct hq_compact_bufs {
+  uint4 *scan;       // n+1 entries: x = passed bytes, y = failed bytes, z = passed reads, w = failed reads (exclusive scan)
+  uint4 *block_sums; // scratch, >= ceil((n+1)/1024) + 1 entries
+  uint8_t *out_seq, *out_qual;
+  uint32_t *out_idx, *out_src; // n+1 / n
+  uint32_t *totals;            // [0]=n_passed [1]=n_failed [2]=passed_bytes [3]=failed_bytes (device)
+};
+cudaError_t hq_launch_compact(const hq_kargs &a, const hq_compact_bufs &b, cudaStream_t st, uint64_t *launches);
+
+cudaError_t hq_launch_synth(const hpgq_synth_cfg_t &cfg, uint64_t first_read, uint32_t n, uint8_t *d_seq,
+                            uint8_t *d_qual, const uint32_t *d_idx, cudaStream_t st, uint64_t *launches);
