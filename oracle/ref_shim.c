@@ -6,6 +6,7 @@
  */
 #include <stdlib.h>
 #include <string.h>
+#include <string.h>
 #include "chaos_game.h" /* the reference header, found via -I/root/reference/old + oracle/ref_stubs */
 
 int ref_chaos_run(int num_reads, char *seq, char *quality, int *data_indices, int *read_status, int mode, int k,
@@ -32,4 +33,12 @@ int ref_chaos_run(int num_reads, char *seq, char *quality, int *data_indices, in
   cg->table_gs = NULL;
   chaos_game_data_free(cg);
   return 0;
+}
+
+/* file_utils helper of the missing common-libs, called by chaos_game_write_table_images
+ * (old/chaos_game.c:416): copy the basename of `path` into `filename`. */
+char *get_filename_from_path(char *path, char *filename) {
+  const char *slash = strrchr(path, '/');
+  strcpy(filename, slash ? slash + 1 : path);
+  return filename;
 }

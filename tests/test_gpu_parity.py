@@ -1,0 +1,237 @@
+"""GPU parity: the CUDA path (through the C ABI) against the CPU oracle on the same seeded inputs.
+Bit-exact for every integer output (counters, histograms, masks, trim coordinates, compacted bytes)."""
+import numpy as np
+import pytest
+
+from test_oracle import (EDIT_OPTS, EDIT_READS, EDIT_TRIM, FILTER_MASK, FILTER_OPTS, FILTER_READS, MICRO, pack,
+                         rand_batch)
+
+pytestmark = pytest.mark.gpu
+
+IGNORE = ("SLOW_READS", "BATCHES", "CG_LONG_RUNS")
+
+
+def diff_report(q, lay, got, exp):
+    bad = np.nonzero(got != exp)[0]
+    ign = {q.S[n] for n in IGNORE}
+    bad = [int(b) for b in bad if int(b) not in ign]
+    if not bad:
+        return ""
+    out = []
+    for b in bad[:12]:
+        sec = max(i for i in range(q.SEC_COUNT) if int(lay.offset[i]) <= b)
+        out.append(f"{q.SEC_NAMES[sec]}[{b - int(lay.offset[sec])}] got {int(got[b])} exp {int(exp[b])}")
+    return f"{len(bad)} words differ: " + "; ".join(out)
+
+
+def run_gpu(q, par, seq, qual, idx, Lcap, kmers=False, k2=0, cg_k=0):
+    n = len(idx) - 1
+    with q.Ctx(0, max_reads=max(n, 1), max_bytes=max(int(idx[-1]), 16), max_read_len=Lcap, kmers=kmers, k2=k2,
+               cg_k=cg_k) as ctx:
+        ctx.set_params(par)
+        ctx.submit(seq, qual, idx, 0)
+        res = ctx.wait(0)
+        return ctx.counters(), res, ctx.layout, ctx.launch_count()
+
+
+def check(q, ob, par, seq, qual, idx, Lcap, **kw):
+    got, res, lay, launches = run_gpu(q, par, seq, qual, idx, Lcap, **kw)
+    exp, emask, etrim = ob.process_batch(par, lay, seq, qual, idx)
+    assert launches > 0
+    assert np.array_equal(res["mask"], emask), f"mask differs at {np.nonzero(res['mask'] != emask)[0][:10]}"
+    if par.work & q.WORK_EDIT:
+        assert np.array_equal(res["trim"], etrim)
+        assert res["n_edited"] == int(exp[q.S["NUM_EDITED"]])
+    msg = diff_report(q, lay, got, exp)
+    assert not msg, msg
+    return got, res, exp, emask, etrim
+
+
+@pytest.mark.parametrize("variant", [0, 1])
+def test_micro_vectors(q, ob, variant):
+    seq, qual, idx = pack(MICRO)
+    check(q, ob, q.make_params(q.WORK_STATS, kernel_variant=variant), seq, qual, idx, 8)
+    seq, qual, idx = pack(FILTER_READS)
+    par = q.make_params(q.WORK_STATS | q.WORK_FILTER, filter=FILTER_OPTS, kernel_variant=variant)
+    _, res, *_ = check(q, ob, par, seq, qual, idx, 8)
+    assert list(res["mask"]) == FILTER_MASK
+
+
+@pytest.mark.parametrize("variant", [0, 1])
+@pytest.mark.parametrize("L", [100, 150, 250, 36, 7])
+def test_stats_filter_fixed_length(q, ob, L, variant):
+    cfg = q.synth_cfg(L)
+    n = 60000 if variant == 0 else 20000
+    seq, qual, idx = q.synth_host(cfg, 0, n)
+    par = q.make_params(q.WORK_STATS | q.WORK_FILTER, kernel_variant=variant,
+                        filter=dict(min_read_length=min(50, L), min_read_quality=20, max_N=5))
+    got, res, exp, *_ = check(q, ob, par, seq, qual, idx, 256)
+    assert 0 < res["n_passed"] < n
+    check(q, ob, q.make_params(q.WORK_STATS, kernel_variant=variant), seq, qual, idx, 256)
+
+
+def test_stats_filter_full_options(q, ob):
+    cfg = q.synth_cfg(150, short_pct=5)
+    seq, qual, idx = q.synth_host(cfg, 7, 50000)
+    flt = dict(min_read_length=60, max_read_length=150, min_read_quality=22, max_read_quality=39,
+               max_out_of_quality=60, left_length=10, min_left_quality=30, max_left_quality=41, right_length=12,
+               min_right_quality=15, max_right_quality=40, max_N=3)
+    for variant in (0, 1):
+        par = q.make_params(q.WORK_STATS | q.WORK_FILTER, filter=flt, kernel_variant=variant)
+        _, res, *_ = check(q, ob, par, seq, qual, idx, 160)
+        assert 0 < res["n_passed"] < 50000
+    par = q.make_params(q.WORK_FILTER, filter=flt)
+    check(q, ob, par, seq, qual, idx, 160)
+
+
+def test_ragged_and_edge_lengths(q, ob):
+    rng = np.random.default_rng(5)
+    seq, qual, idx = rand_batch(rng, 30000, 0, 130, p_n=0.03)
+    par = q.make_params(q.WORK_STATS | q.WORK_FILTER, filter=dict(min_read_length=20, min_read_quality=18, max_N=4,
+                                                                  left_length=200, min_left_quality=19))
+    check(q, ob, par, seq, qual, idx, 130)
+    # empty batch, single read, all-empty reads
+    for reads in ([], [(b"ACGT", b"IIII")], [(b"", b"")] * 5):
+        s, ql, ix = pack(reads)
+        check(q, ob, q.make_params(q.WORK_STATS | q.WORK_FILTER, filter=dict(max_N=1)), s, ql, ix, 16)
+    # maximum length of the tiled kernel (640) and just beyond it (falls to the warp-per-read kernel)
+    for L in (640, 641, 3000):
+        seq, qual, idx = q.synth_host(q.synth_cfg(L), 0, 700)
+        check(q, ob, q.make_params(q.WORK_STATS | q.WORK_FILTER, filter=dict(min_read_quality=20)), seq, qual, idx, L)
+
+
+def test_lowercase_and_foreign_bytes_take_exact_path(q, ob):
+    cfg = q.synth_cfg(100, lowercase_ppm=2000)
+    seq, qual, idx = q.synth_host(cfg, 0, 40000)
+    seq = seq.copy()
+    seq[12345] = ord("R")
+    seq[777] = 0xC3
+    qual = qual.copy()
+    qual[4321] = 200
+    par = q.make_params(q.WORK_STATS | q.WORK_FILTER, filter=dict(min_read_quality=20, max_read_quality=40,
+                                                                  max_out_of_quality=30, max_N=5))
+    got, *_ = check(q, ob, par, seq, qual, idx, 128)
+    assert got[q.S["SLOW_READS"]] > 0
+
+
+def test_phred64(q, ob):
+    cfg = q.synth_cfg(100)
+    seq, qual, idx = q.synth_host(cfg, 0, 20000)
+    qual = (qual + 31).astype(np.uint8)
+    par = q.make_params(q.WORK_STATS | q.WORK_FILTER, phred=64, filter=dict(min_read_quality=20, max_N=5))
+    check(q, ob, par, seq, qual, idx, 128)
+
+
+def test_multi_batch_accumulation_and_slots(q, ob):
+    cfg = q.synth_cfg(150)
+    par = q.make_params(q.WORK_STATS | q.WORK_FILTER, filter=dict(min_read_length=50, min_read_quality=20, max_N=5))
+    n, nb = 30000, 5
+    with q.Ctx(0, max_reads=n, max_bytes=n * 150, max_read_len=160, n_slots=2) as ctx:
+        ctx.set_params(par)
+        lay = ctx.layout
+        exp = np.zeros(lay.words, dtype=np.uint64)
+        masks = {}
+        for b in range(nb):
+            slot = b % 2
+            if b >= 2:
+                masks[b - 2] = ctx.wait(slot)["mask"]
+            seq, qual, idx = q.synth_host(cfg, b * n, n)
+            ctx.submit(seq, qual, idx, slot)
+            exp, emask, _ = ob.process_batch(par, lay, seq, qual, idx, counters=exp, finalize=False)
+            masks[("e", b)] = emask
+        for b in range(nb - 2, nb):
+            masks[b] = ctx.wait(b % 2)["mask"]
+        got = ctx.counters()
+    ob.lib().oracle_finalize(__import__("ctypes").byref(lay), exp.ctypes.data_as(__import__("ctypes").c_void_p))
+    for b in range(nb):
+        assert np.array_equal(masks[b], masks[("e", b)])
+    msg = diff_report(q, lay, got, exp)
+    assert not msg, msg
+
+
+def test_device_resident_generator_matches_host(q, ob):
+    cfg = q.synth_cfg(150, short_pct=2)
+    n = 50000
+    seq, qual, idx = q.synth_host(cfg, 123, n)
+    par = q.make_params(q.WORK_STATS | q.WORK_FILTER, filter=dict(min_read_length=50, min_read_quality=20, max_N=5))
+    with q.Ctx(0, max_reads=n, max_bytes=n * 150, max_read_len=160, host_staging=False) as ctx:
+        ctx.set_params(par)
+        b = ctx.synth_device(cfg, 123, n)
+        assert b.n_bytes == int(idx[-1])
+        assert np.array_equal(ctx.dev_download(b.seq, b.n_bytes), seq)
+        assert np.array_equal(ctx.dev_download(b.qual, b.n_bytes), qual)
+        for hint in (None, 0):  # with the caller's max-length hint and with the on-device measurement
+            ctx.counters_reset()
+            ctx.submit_device(b, 0, max_len_hint=hint)
+            ctx.sync(0)
+            got = ctx.counters()
+            assert ctx.last_kernel_ms(0) > 0
+            exp, *_ = ob.process_batch(par, ctx.layout, seq, qual, idx)
+            msg = diff_report(q, ctx.layout, got, exp)
+            assert not msg, msg
+        ctx.free_batch(b)
+
+
+def test_edit_trim_filter_compact(q, ob):
+    seq, qual, idx = pack(EDIT_READS)
+    par = q.make_params(q.WORK_EDIT | q.WORK_FILTER | q.WORK_COMPACT, edit=EDIT_OPTS, filter=dict(min_read_length=3))
+    _, res, _, emask, etrim = check(q, ob, par, seq, qual, idx, 8)
+    assert [tuple(int(x) for x in t) for t in res["trim"]] == EDIT_TRIM
+    assert bytes(res["out_seq"]) == b"GTACACGTAC"
+    cfg = q.synth_cfg(150, short_pct=3)
+    seq, qual, idx = q.synth_host(cfg, 0, 80000)
+    for work, flt in ((q.WORK_EDIT | q.WORK_FILTER | q.WORK_COMPACT, dict(min_read_length=50, min_read_quality=20, max_N=5)),
+                      (q.WORK_EDIT | q.WORK_COMPACT, None), (q.WORK_FILTER | q.WORK_COMPACT, dict(min_read_quality=25))):
+        par = q.make_params(work, edit=dict(left_length=10, min_left_quality=34, right_length=10, min_right_quality=20),
+                            filter=flt)
+        _, res, _, emask, etrim = check(q, ob, par, seq, qual, idx, 160)
+        cp = ob.compact(seq, qual, idx, emask if work & q.WORK_FILTER else None, etrim if work & q.WORK_EDIT else None)
+        assert res["n_passed"] == cp["n_passed"] and res["passed_bytes"] == cp["passed_bytes"]
+        assert res["failed_bytes"] == cp["failed_bytes"]
+        for k in ("out_idx", "out_src", "out_seq", "out_qual"):
+            assert np.array_equal(res[k], cp[k]), k
+
+
+def test_kmers_and_chaos_game(q, ob):
+    seq, qual, idx = pack([(b"ACGTANGTACGT", b"I" * 12)])
+    check(q, ob, q.make_params(q.WORK_KMERS, k2=3), seq, qual, idx, 16, kmers=True, k2=3)
+    cfg = q.synth_cfg(250, cap_axis_runs=1)
+    seq, qual, idx = q.synth_host(cfg, 0, 20000)
+    par = q.make_params(q.WORK_STATS | q.WORK_FILTER | q.WORK_KMERS | q.WORK_CHAOS, k2=11, cg_k=10,
+                        filter=dict(min_read_quality=20, max_N=5))
+    got, *_ = check(q, ob, par, seq, qual, idx, 256, kmers=True, k2=11, cg_k=10)
+    assert got[q.S["CG_LONG_RUNS"]] == 0
+    # lower-case bytes: literal positional quality window of old/chaos_game.c:259
+    rng = np.random.default_rng(11)
+    seq, qual, idx = rand_batch(rng, 3000, 0, 90, p_n=0.02, lower=0.01)
+    par = q.make_params(q.WORK_KMERS | q.WORK_CHAOS, k2=6, cg_k=5)
+    check(q, ob, par, seq, qual, idx, 96, kmers=True, k2=6, cg_k=5)
+    # a long axis run is reported (float and integer chaos-game indices may differ there)
+    seq, qual, idx = pack([(b"T" * 70, b"I" * 70), (b"CCCCCCCCCCCCACGT", b"I" * 16)])
+    got, _, lay, _ = run_gpu(q, q.make_params(q.WORK_CHAOS, cg_k=10), seq, qual, idx, 96, cg_k=10)
+    assert got[q.S["CG_LONG_RUNS"]] > 0
+
+
+def test_checksum_of_checksums_full_shape(q, ob):
+    """Size-independent property at a bench-sized batch: column sums of the per-position tables equal the
+    length histogram's suffix sums, base totals add up to the passed bases."""
+    cfg = q.synth_cfg(150)
+    n = 2_000_000
+    par = q.make_params(q.WORK_STATS | q.WORK_FILTER, filter=dict(min_read_length=50, min_read_quality=20, max_N=5))
+    with q.Ctx(0, max_reads=n, max_bytes=n * 150, max_read_len=160, host_staging=False) as ctx:
+        ctx.set_params(par)
+        b = ctx.synth_device(cfg, 0, n)
+        ctx.submit_device(b, 0)
+        ctx.sync(0)
+        c = ctx.counters()
+        lay = ctx.layout
+        ctx.free_batch(b)
+    S = q.S
+    assert c[S["NUM_PASSED"]] + c[S["NUM_FAILED"]] == n and c[S["NUM_READS"]] == c[S["NUM_PASSED"]]
+    lh = lay.section(c, "LEN_HIST").astype(np.int64)
+    count_per_pos = lh[::-1].cumsum()[::-1][1:]  # reads with length > p
+    tot = sum(lay.section(c, k).astype(np.int64) for k in ("POS_A", "POS_C", "POS_G", "POS_T", "POS_N"))
+    assert np.array_equal(tot, count_per_pos[:len(tot)])
+    assert sum(int(c[S[k]]) for k in ("NUM_A", "NUM_C", "NUM_G", "NUM_T", "NUM_N")) == int(c[S["ACC_LENGTH"]])
+    assert int(lay.section(c, "SUMQ_BY_LEN").sum()) == int(lay.section(c, "POS_ACCQ").sum())
+    assert int(lay.section(c, "QUAL_HIST").sum()) == int(c[S["NUM_READS"]]) == int(lay.section(c, "GC_HIST").sum())
