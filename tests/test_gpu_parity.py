@@ -37,7 +37,7 @@ def run_gpu(q, par, seq, qual, idx, Lcap, kmers=False, k2=0, cg_k=0):
 def check(q, ob, par, seq, qual, idx, Lcap, **kw):
     got, res, lay, launches = run_gpu(q, par, seq, qual, idx, Lcap, **kw)
     exp, emask, etrim = ob.process_batch(par, lay, seq, qual, idx)
-    assert launches > 0
+    assert launches > 0 or len(idx) == 1  # an empty batch launches nothing
     assert np.array_equal(res["mask"], emask), f"mask differs at {np.nonzero(res['mask'] != emask)[0][:10]}"
     if par.work & q.WORK_EDIT:
         assert np.array_equal(res["trim"], etrim)
