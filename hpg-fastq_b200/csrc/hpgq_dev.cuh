@@ -109,6 +109,62 @@ HQ_HDI hq_dec_t hq_decode_exact(uint32_t sw) {
   return d;
 }
 
+// ------------------------------------------------------------------ nibble-LUT decoding (tiled kernel v2)
+// Natural byte order (output byte i <-> input byte i): the word is byte-swapped (1 <-> 2) BEFORE the
+// selector is formed, so t + (t >> 12) yields the nibbles in input order.  Two LUTs give packed
+// 4-bit one-hots: cg = C->0x01, G->0x10 ; at = A->0x01, T->0x10.  N (and only N) is a valid byte
+// with no count: per-read N = L - #ACGT, so bytes past the read end are FILLED with 'N' (hq_fill_n)
+// instead of zeroed, and 0x00 inside a read is flagged bad like any other foreign byte.
+struct hq_dec2_t {
+  uint32_t cg, at;
+  uint32_t bad; // non-zero iff some byte is not one of A,C,G,T,N
+};
+
+// (sw & m) | (~m & "NNNN") : one LOP3
+HQ_HDI uint32_t hq_fill_n(uint32_t sw, uint32_t m) { return (sw & m) | (~m & 0x4E4E4E4Eu); }
+
+HQ_HDI hq_dec2_t hq_decode2(uint32_t swm) {
+  hq_dec2_t d;
+  const uint32_t wp = hq_prmt(swm, 0u, 0x3120u);
+  const uint32_t s = hq_selector(wp);
+  d.cg = hq_prmt(0x01000000u, 0x10000000u, s);
+  d.at = hq_prmt(0x00000100u, 0x00000010u, s);
+  const uint32_t e = hq_prmt(0x43FF41FFu, 0x474EFF54u, s);
+  d.bad = swm ^ e;
+  return d;
+}
+
+// exact per-byte twin for words holding foreign bytes; only bytes selected by m are looked at.
+// other = 0x01 per in-read byte that is none of A,C,G,T,N
+HQ_HDI hq_dec2_t hq_decode2_exact(uint32_t sw, uint32_t m, uint32_t *other) {
+  hq_dec2_t d;
+  d.cg = d.at = d.bad = 0u;
+  uint32_t oth = 0u;
+  for (int i = 0; i < 4; ++i) {
+    if (!((m >> (8 * i)) & 1u)) continue;
+    const uint32_t c = (sw >> (8 * i)) & 0xFFu;
+    if (c == 'C') d.cg |= 0x01u << (8 * i);
+    else if (c == 'G') d.cg |= 0x10u << (8 * i);
+    else if (c == 'A') d.at |= 0x01u << (8 * i);
+    else if (c == 'T') d.at |= 0x10u << (8 * i);
+    else if (c != 'N') oth |= 0x01u << (8 * i);
+  }
+  *other = oth;
+  return d;
+}
+
+// sum over the four bytes of the low+high nibble of each byte (fields <= 7 each)
+HQ_HDI uint32_t hq_nibble_total(uint32_t x) { return hq_dp4a((x + (x >> 4)) & 0x0F0F0F0Fu, 0x01010101u, 0u); }
+
+// exact x / d for x < 2^22, d >= 1, from a float reciprocal of d (any rounding); ~8 instructions
+HQ_HDI uint32_t hq_udiv_rcp(uint32_t x, uint32_t d, float rcp) {
+  uint32_t q = (uint32_t)((float)x * rcp);
+  const int32_t r = (int32_t)(x - q * d);
+  if (r < 0) --q;
+  else if (r >= (int32_t)d) ++q;
+  return q;
+}
+
 // quality word -> two words of 16-bit lanes: lo = (byte0, byte2), hi = (byte1, byte3)
 HQ_HDI uint32_t hq_q16_lo(uint32_t qw) { return hq_prmt(qw, 0u, 0x4240u); }
 HQ_HDI uint32_t hq_q16_hi(uint32_t qw) { return hq_prmt(qw, 0u, 0x4341u); }
