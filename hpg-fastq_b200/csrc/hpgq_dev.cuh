@@ -28,6 +28,18 @@ HQ_HDI uint32_t hq_prmt(uint32_t a, uint32_t b, uint32_t s) {
 #endif
 }
 
+// PRMT without the (s & 0x7777) that __byte_perm's contract forces the compiler to emit: only for
+// selectors whose nibbles are known to be <= 7 (bits above 15 are ignored by the instruction)
+HQ_HDI uint32_t hq_prmt_raw(uint32_t a, uint32_t b, uint32_t s) {
+#ifdef __CUDA_ARCH__
+  uint32_t r;
+  asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(s));
+  return r;
+#else
+  return hq_prmt(a, b, s & 0x7777u);
+#endif
+}
+
 HQ_HDI uint32_t hq_dp4a(uint32_t a, uint32_t b, uint32_t c) {
 #ifdef __CUDA_ARCH__
   return __dp4a(a, b, c);
@@ -127,9 +139,9 @@ HQ_HDI hq_dec2_t hq_decode2(uint32_t swm) {
   hq_dec2_t d;
   const uint32_t wp = hq_prmt(swm, 0u, 0x3120u);
   const uint32_t s = hq_selector(wp);
-  d.cg = hq_prmt(0x01000000u, 0x10000000u, s);
-  d.at = hq_prmt(0x00000100u, 0x00000010u, s);
-  const uint32_t e = hq_prmt(0x43FF41FFu, 0x474EFF54u, s);
+  d.cg = hq_prmt_raw(0x01000000u, 0x10000000u, s);
+  d.at = hq_prmt_raw(0x00000100u, 0x00000010u, s);
+  const uint32_t e = hq_prmt_raw(0x43FF41FFu, 0x474EFF54u, s);
   d.bad = swm ^ e;
   return d;
 }
@@ -212,6 +224,23 @@ HQ_DI void hq_mbar_wait(uint64_t *bar, uint32_t parity) {
         : "r"(a), "r"(parity)
         : "memory");
   } while (!ok);
+}
+// same, for a lone thread that is expected to wait long (the producer): sleeps between polls so that it
+// does not steal issue slots from the warps that share its scheduler
+HQ_DI void hq_mbar_wait_backoff(uint64_t *bar, uint32_t parity) {
+  const uint32_t a = hq_smem_u32(bar);
+  uint32_t ok;
+  for (;;) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(a), "r"(parity)
+        : "memory");
+    if (ok) break;
+    __nanosleep(100);
+  }
 }
 // 1-D bulk async copy global -> shared (TMA engine, SASS UBLKCP); 16-byte aligned, size % 16 == 0
 HQ_DI void hq_bulk_g2s(void *dst_smem, const void *src_gmem, uint32_t bytes, uint64_t *bar) {

@@ -36,6 +36,7 @@ struct hq_kargs {
   uint32_t G;           // lanes per read group
   uint32_t stage_bytes; // capacity of one seq (and one qual) stage buffer
   uint32_t n_tiles;
+  uint32_t n_stages;    // depth of the shared-memory ring
 };
 
 // launchers (return cudaGetLastError()); `launches` is incremented per kernel launched

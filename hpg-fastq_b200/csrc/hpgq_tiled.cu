@@ -1,6 +1,7 @@
 // hpgq_tiled.cu -- geometry selection and dispatch of the tiled stats+filter kernel (hpgq_tiled.cuh).
 // The kernel is instantiated for a fixed list of (K words per lane, G lanes per read) pairs in
 // hpgq_tiled_g*.cu; the launcher picks the pair with the best lane utilisation for the batch's longest read.
+#include <stdlib.h>
 #include "hpgq_tiled.cuh"
 
 namespace {
@@ -16,10 +17,21 @@ const geom_entry kGeoms[] = {{2, 4}, {3, 4}, {4, 4}, {5, 4}, {5, 5}, {3, 8}, {4,
 
 struct hq_geom {
   int K, G;
-  uint32_t RT, stage_bytes, smem_bytes;
+  uint32_t RT, NS, stage_bytes, smem_bytes;
 };
 
+// tuning knobs (defaults measured on B200): HPGQ_TILE_BYTES = bases per tile that stop
+// the growth of RT, HPGQ_STAGES = ring depth
+uint32_t env_u32(const char *name, uint32_t dflt, uint32_t lo, uint32_t hi) {
+  const char *v = getenv(name);
+  if (!v || !*v) return dflt;
+  const long x = strtol(v, nullptr, 10);
+  return x < (long)lo ? lo : (x > (long)hi ? hi : (uint32_t)x);
+}
+
 bool pick_geom(uint32_t max_len, uint32_t n_reads, int sm_count, size_t smem_limit, hq_geom *out) {
+  const uint32_t NS = env_u32("HPGQ_STAGES", 3, 2, NSMAX);
+  const uint32_t tile_bytes = env_u32("HPGQ_TILE_BYTES", 26 * 1024, 1024, 64 * 1024);
   if (max_len == 0) max_len = 1;
   const uint32_t words = (max_len + 3u) / 4u;
   double best = -1.0;
@@ -48,7 +60,7 @@ bool pick_geom(uint32_t max_len, uint32_t n_reads, int sm_count, size_t smem_lim
     const size_t need = idx_cap_bytes(cand) + 2ull * ((((size_t)cand * max_len + 48u + pad) + 127u) & ~127ull);
     if (need > budget) break;
     RT = cand;
-    if ((size_t)cand * max_len >= 26u * 1024u) break;  // big enough to amortise the barriers
+    if ((size_t)cand * max_len >= tile_bytes) break;  // big enough to amortise the barriers
   }
   if (!RT) return false;
   // small batches: keep at least ~2 tiles per SM so the grid is balanced
@@ -57,6 +69,7 @@ bool pick_geom(uint32_t max_len, uint32_t n_reads, int sm_count, size_t smem_lim
   out->K = bK;
   out->G = bG;
   out->RT = RT;
+  out->NS = NS;
   out->stage_bytes = (uint32_t)((((size_t)RT * max_len + 48u + pad) + 127u) & ~127ull);
   out->smem_bytes = SM_STAGES + NS * (idx_cap_bytes(RT) + 2u * out->stage_bytes);
   return true;
@@ -82,6 +95,8 @@ cudaError_t hq_launch_qc_tiled(hq_kargs a, uint32_t max_len_in_batch, int sm_cou
       !pick_geom(max_len_in_batch, a.n_reads, sm_count, 227 * 1024, &gm))
     return cudaErrorInvalidValue;
   a.RT = gm.RT;
+  if (getenv("HPGQ_DEBUG_LOADONLY")) a.work |= 0x8000u;  // developer probe: ring traffic without the arithmetic
+  a.n_stages = gm.NS;
   a.G = (uint32_t)gm.G;
   a.stage_bytes = gm.stage_bytes;
   a.n_tiles = (a.n_reads + gm.RT - 1u) / gm.RT;

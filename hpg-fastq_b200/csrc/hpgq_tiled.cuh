@@ -25,15 +25,15 @@
 
 namespace hqt {
 
-constexpr int NS = 3;                    // pipeline stages
+constexpr int NSMAX = 8;                 // pipeline stages are a launch parameter (hq_kargs.n_stages <= NSMAX)
 constexpr int NCW = 15;                  // consumer warps (15 + producer = 4 warps per SM sub-partition: 128 registers each)
 constexpr int THREADS = (NCW + 1) * 32;  // + 1 producer warp
 constexpr int TAB = 640;                 // positions held by the block-private tables
 constexpr int KMAX = 5;
 
 // fixed shared-memory carve-up (bytes)
-constexpr uint32_t SM_BAR = 0;                               // full[NS], empty[NS]
-constexpr uint32_t SM_TAB = 64;                              // u32 [6][TAB]: accq, A, C, G, T, other
+constexpr uint32_t SM_BAR = 0;                               // full[NSMAX], empty[NSMAX]
+constexpr uint32_t SM_TAB = 128;                             // u32 [6][TAB]: accq, A, C, G, T, other
 constexpr uint32_t SM_LEN = SM_TAB + 4u * 6u * TAB;          // u32 [TAB + 4]
 constexpr uint32_t SM_QH = SM_LEN + 4u * (TAB + 4);          // u32 [256]
 constexpr uint32_t SM_GC = SM_QH + 4u * 256u;                // u32 [104]
