@@ -67,6 +67,10 @@ struct hpgq_ctx {
   hpgq_slot slot[HPGQ_MAX_SLOTS];
   uint64_t launches = 0;
   uint64_t batches = 0;
+  // ev1 of the most recent batch on any slot: the next batch's kernels wait for it, so that kernels of
+  // different slots never queue behind each other inside an ev0..ev1 bracket (each QC kernel fills every SM
+  // anyway).  Copies of the next batch still overlap the running kernel.
+  cudaEvent_t last_done = nullptr;
 };
 
 // ------------------------------------------------------------------ misc

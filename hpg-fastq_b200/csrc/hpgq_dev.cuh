@@ -146,6 +146,24 @@ HQ_HDI hq_dec2_t hq_decode2(uint32_t swm) {
   return d;
 }
 
+// same as hq_decode2 with the selector's shift-add issued as one IMAD.HI: p20 must be 2^20, passed through a
+// kernel argument so that the compiler cannot turn it back into LEA.HI (ALU pipe)
+HQ_HDI hq_dec2_t hq_decode2_fma(uint32_t swm, uint32_t p20) {
+  hq_dec2_t d;
+  const uint32_t wp = hq_prmt_raw(swm, 0u, 0x3120u);
+  const uint32_t t = wp & 0x07070707u;
+#ifdef __CUDA_ARCH__
+  const uint32_t s = __umulhi(t, p20) + t;
+#else
+  const uint32_t s = (uint32_t)(((uint64_t)t * p20) >> 32) + t;
+#endif
+  d.cg = hq_prmt_raw(0x01000000u, 0x10000000u, s);
+  d.at = hq_prmt_raw(0x00000100u, 0x00000010u, s);
+  const uint32_t e = hq_prmt_raw(0x43FF41FFu, 0x474EFF54u, s);
+  d.bad = swm ^ e;
+  return d;
+}
+
 // exact per-byte twin for words holding foreign bytes; only bytes selected by m are looked at.
 // other = 0x01 per in-read byte that is none of A,C,G,T,N
 HQ_HDI hq_dec2_t hq_decode2_exact(uint32_t sw, uint32_t m, uint32_t *other) {

@@ -37,6 +37,10 @@ struct hq_kargs {
   uint32_t stage_bytes; // capacity of one seq (and one qual) stage buffer
   uint32_t n_tiles;
   uint32_t n_stages;    // depth of the shared-memory ring
+  // multipliers the compiler cannot see through (1, 2^20, 2^24): `x * one + y`, `umulhi(x, p20) + y` stay
+  // IMAD / IMAD.HI on the FMA pipe instead of being strength-reduced to IADD3 / SHF / LEA.HI on the ALU
+  // pipe, which is the busiest unit of the tiled kernel (profiles/tiled_r1b_summary.md)
+  uint32_t one, p20, p24;
 };
 
 // launchers (return cudaGetLastError()); `launches` is incremented per kernel launched

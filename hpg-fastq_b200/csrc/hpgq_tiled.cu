@@ -97,6 +97,9 @@ cudaError_t hq_launch_qc_tiled(hq_kargs a, uint32_t max_len_in_batch, int sm_cou
   a.RT = gm.RT;
   if (getenv("HPGQ_DEBUG_LOADONLY")) a.work |= 0x8000u;  // developer probe: ring traffic without the arithmetic
   a.n_stages = gm.NS;
+  a.one = 1u;
+  a.p20 = 1u << 20;
+  a.p24 = 1u << 24;
   a.G = (uint32_t)gm.G;
   a.stage_bytes = gm.stage_bytes;
   a.n_tiles = (a.n_reads + gm.RT - 1u) / gm.RT;

@@ -26,7 +26,10 @@
 namespace hqt {
 
 constexpr int NSMAX = 8;                 // pipeline stages are a launch parameter (hq_kargs.n_stages <= NSMAX)
-constexpr int NCW = 15;                  // consumer warps (15 + producer = 4 warps per SM sub-partition: 128 registers each)
+#ifndef HQ_NCW
+#define HQ_NCW 15
+#endif
+constexpr int NCW = HQ_NCW;                 // consumer warps (15 + producer = 4 warps per SM sub-partition: 128 registers each)
 constexpr int THREADS = (NCW + 1) * 32;  // + 1 producer warp
 constexpr int TAB = 640;                 // positions held by the block-private tables
 constexpr int KMAX = 5;

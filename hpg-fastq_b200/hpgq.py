@@ -113,10 +113,11 @@ def load_library() -> C.CDLL:
     global _lib
     if _lib is not None:
         return _lib
-    if not os.path.exists(LIB_PATH):
-        raise HpgqError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+    path = os.environ.get("HPGQ_LIB", LIB_PATH)  # developer A/B of kernel variants (tools/); default = in-tree build
+    if not os.path.exists(path):
+        raise HpgqError(f"{path} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
                         "(make -C hpg-fastq_b200/csrc). There is no CPU fallback.")
-    lib = C.CDLL(LIB_PATH)
+    lib = C.CDLL(path)
     for name in ("hpgq_strerror", "hpgq_last_error", "hpgq_version"):
         getattr(lib, name).restype = C.c_char_p
     lib.hpgq_strerror.argtypes = [C.c_int]
