@@ -334,3 +334,4 @@ extern "C" int hpgq_host_free_pinned(void *ptr) {
 }
 
 #include "hpgq_api_batch.inc"
+#include "hpgq_api_reduce.inc"

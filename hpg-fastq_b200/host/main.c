@@ -1,0 +1,358 @@
+/*
+ * main.c -- `hpg-fastq stats|filter|edit`: the reference's command line (src/hpg-fastq.c:38-127) over the
+ * B200 C ABI.  The workflow of each command keeps the reference's shape
+ *   producer  fastq_*_producer  (src/stats_fastq.c:174-196)  -> hq_reader_next: FASTQ text -> pinned SoA batch
+ *   worker    fastq_*_worker    (src/stats_fastq.c:202-251, src/filter_fastq.c:134-155, src/edit_fastq.c:142-178)
+ *                                                             -> hpgq_batch_submit (H2D + kernels, async)
+ *   consumer  fastq_*_consumer  (src/stats_fastq.c:257-417, src/filter_fastq.c:161-176, src/edit_fastq.c:184-208)
+ *                                                             -> hpgq_batch_wait + ordered FASTQ writer;
+ *                                                                the statistics merge stays on the device
+ * with batch b on GPU b mod N, stream slot (b / N) mod 2, so that parsing batch b+1 overlaps the copies and
+ * kernels of batch b, and outputs are written in ascending batch order (= input order).
+ * There is no CPU fallback: without a B200 the program stops with the library's error.
+ */
+#include "hpgq_host.h"
+
+#include <stdlib.h>
+#include <string.h>
+#include <time.h>
+
+#define HQ_SLOTS 2
+#define HQ_MAX_GPUS 16
+
+static FILE *g_log;
+
+static void logf_(const char *level, const char *msg) {
+  if (g_log) {
+    fprintf(g_log, "%s: %s\n", level, msg);
+    fflush(g_log);
+  }
+}
+
+static int die_hpgq(const char *what, int rc) {
+  char buf[768];
+  snprintf(buf, sizeof buf, "%s: %s [%d] -- %s", what, hpgq_strerror(rc), rc, hpgq_last_error());
+  fprintf(stderr, "\nFATAL: %s\n", buf);
+  logf_("FATAL", buf);
+  return 1;
+}
+
+static void usage(const char *exec_name) {
+  /* usage(), src/hpg-fastq.c:17-31 */
+  printf("Program: %s (High-performance tools for handling FastQ files)\n", exec_name);
+  printf("Version: 1.0.0\n");
+  printf("\n");
+  printf("Usage: %s <command> [options]\n", exec_name);
+  printf("\n");
+  printf("Command: stats\t\tstatistics summary\n");
+  printf("         filter\t\tfilter a FastQ file by using advanced criteria\n");
+  printf("         edit\t\tedit a FastQ file according the specified options\n");
+  printf("\n");
+  printf("For more information about a certain command, type %s <command> --help\n", exec_name);
+}
+
+typedef struct run {
+  hq_options_t *o;
+  hq_reader_t *reader;
+  int n_gpus;
+  hpgq_ctx_t *ctx[HQ_MAX_GPUS];
+  hq_host_batch_t hb[HQ_MAX_GPUS][HQ_SLOTS];
+  int busy[HQ_MAX_GPUS][HQ_SLOTS];
+  hq_writer_t *w_pass, *w_fail;
+  uint64_t num_passed, num_failed, num_edited, num_reads;
+} run_t;
+
+static int alloc_host_batch(hq_host_batch_t *b, uint32_t cap_reads, uint64_t cap_bytes) {
+  memset(b, 0, sizeof *b);
+  b->cap_reads = cap_reads;
+  b->cap_bytes = cap_bytes;
+  int rc;
+  if ((rc = hpgq_host_alloc_pinned(cap_bytes + 64, (void **)&b->seq))) return rc;
+  if ((rc = hpgq_host_alloc_pinned(cap_bytes + 64, (void **)&b->qual))) return rc;
+  if ((rc = hpgq_host_alloc_pinned(((size_t)cap_reads + 1) * 4 + 64, (void **)&b->idx))) return rc;
+  b->hdr_off = (uint64_t *)malloc((size_t)cap_reads * sizeof(uint64_t));
+  b->hdr_len = (uint32_t *)malloc((size_t)cap_reads * sizeof(uint32_t));
+  return (b->hdr_off && b->hdr_len) ? 0 : HPGQ_ERR_NOMEM;
+}
+
+static void free_host_batch(hq_host_batch_t *b) {
+  if (b->seq) hpgq_host_free_pinned(b->seq);
+  if (b->qual) hpgq_host_free_pinned(b->qual);
+  if (b->idx) hpgq_host_free_pinned(b->idx);
+  free(b->hdr_off);
+  free(b->hdr_len);
+  memset(b, 0, sizeof *b);
+}
+
+/* consumer stage for one retired slot */
+static int consume(run_t *r, int g, int s) {
+  hpgq_batch_result_t res;
+  int rc = hpgq_batch_wait(r->ctx[g], s, &res);
+  if (rc) return die_hpgq("hpgq_batch_wait", rc);
+  r->busy[g][s] = 0;
+  const hq_options_t *o = r->o;
+  const hq_host_batch_t *b = &r->hb[g][s];
+  const uint8_t *fd = hq_reader_data(r->reader);
+  r->num_reads += res.n_reads;
+  if (o->command == HQ_CMD_STATS) return 0; /* counters stay on the device */
+  r->num_edited += res.n_edited;
+  const int filtering = o->command == HQ_CMD_FILTER || o->filter_on;
+  if (filtering) {
+    /* passed reads [0, n_passed) then failed reads, each in input order (src/filter_fastq.c:165-169) */
+    r->num_passed += res.n_passed;
+    r->num_failed += res.n_failed;
+    if (hq_writer_put(r->w_pass, fd, b, res.out_seq, res.out_qual, res.out_idx, res.out_src, 0, res.n_passed) ||
+        hq_writer_put(r->w_fail, fd, b, res.out_seq, res.out_qual, res.out_idx, res.out_src, res.n_passed,
+                      res.n_passed + res.n_failed)) {
+      fprintf(stderr, "\nFATAL: write error on the output FASTQ files\n");
+      return 1;
+    }
+  } else {
+    /* edit without filter options: every (trimmed) read goes to edit.fq (src/edit_fastq.c:196-199) */
+    if (hq_writer_put(r->w_pass, fd, b, res.out_seq, res.out_qual, res.out_idx, res.out_src, 0, res.n_reads)) {
+      fprintf(stderr, "\nFATAL: write error on the output FASTQ file\n");
+      return 1;
+    }
+  }
+  return 0;
+}
+
+static int run_pipeline(run_t *r) {
+  const int N = r->n_gpus;
+  uint64_t b = 0;
+  for (;; b++) {
+    const int g = (int)(b % (uint64_t)N), s = (int)((b / (uint64_t)N) % HQ_SLOTS);
+    if (r->busy[g][s] && consume(r, g, s)) return 1;
+    hq_host_batch_t *hb = &r->hb[g][s];
+    int got = hq_reader_next(r->reader, hb);
+    if (got < 0) {
+      fprintf(stderr, "\nFATAL: %s: %s\n", r->o->in_filename, hq_reader_error(r->reader));
+      logf_("FATAL", hq_reader_error(r->reader));
+      return 1;
+    }
+    if (!got) break;
+    hpgq_batch_t hbatch = {hb->n_reads, 0, hb->seq, hb->qual, hb->idx};
+    int rc = hpgq_batch_submit(r->ctx[g], &hbatch, s);
+    if (rc) return die_hpgq("hpgq_batch_submit", rc);
+    r->busy[g][s] = 1;
+  }
+  /* drain in batch order: the oldest outstanding batch is b - N*HQ_SLOTS */
+  const uint64_t first = b > (uint64_t)N * HQ_SLOTS ? b - (uint64_t)N * HQ_SLOTS : 0;
+  for (uint64_t k = first; k < b; k++) {
+    const int g = (int)(k % (uint64_t)N), s = (int)((k / (uint64_t)N) % HQ_SLOTS);
+    if (r->busy[g][s] && consume(r, g, s)) return 1;
+  }
+  return 0;
+}
+
+static double now_s(void) {
+  struct timespec ts;
+  clock_gettime(CLOCK_MONOTONIC, &ts);
+  return (double)ts.tv_sec + 1e-9 * (double)ts.tv_nsec;
+}
+
+static int run_command(hq_options_t *o) {
+  run_t *r = (run_t *)calloc(1, sizeof *r);
+  if (!r) return 1;
+  r->o = o;
+  int status = 1, rc;
+  char pass_name[4096] = "", fail_name[4096] = "";
+  const double t0 = now_s();
+
+  /* "update opts": NO_VALUE -> MIN/MAX (stats only when a filter option was given, src/stats_fastq.c:430-444) */
+  if (o->command != HQ_CMD_STATS || o->filter_on) hq_options_fill_unset(o);
+
+  if (hq_reader_open(o->in_filename, &r->reader)) {
+    fprintf(stderr, "\nFATAL: cannot open %s\n", o->in_filename);
+    goto out;
+  }
+  /* Lcap (entries of the per-position tables) and the batch byte capacity come from the longest line */
+  uint32_t max_line = (uint32_t)o->max_read_len;
+  if (max_line == 0) {
+    uint64_t n_lines = 0;
+    if (hq_reader_scan(r->reader, &max_line, &n_lines)) {
+      fprintf(stderr, "\nFATAL: %s holds a line longer than 4 GiB\n", o->in_filename);
+      goto out;
+    }
+  }
+  if (max_line == 0) max_line = 1;
+  uint64_t cap_bytes = (uint64_t)o->batch_size * max_line;
+  if (cap_bytes > (1ull << 30)) cap_bytes = 1ull << 30; /* batches are cut by bytes first for long reads */
+  if (cap_bytes < max_line) cap_bytes = max_line;
+  if (cap_bytes < 4096) cap_bytes = 4096;
+
+  int ndev = 0;
+  rc = hpgq_device_count(&ndev);
+  if (rc || ndev < 1) {
+    die_hpgq("hpgq_device_count", rc ? rc : HPGQ_ERR_NO_DEVICE);
+    goto out;
+  }
+  r->n_gpus = o->gpus;
+  if (r->n_gpus > ndev) {
+    fprintf(stderr, "\nFATAL: --gpus %d but only %d CUDA device(s) are visible\n", o->gpus, ndev);
+    goto out;
+  }
+  hpgq_params_t par;
+  hq_options_to_params(o, &par);
+  hpgq_limits_t lim;
+  memset(&lim, 0, sizeof lim);
+  lim.max_reads_per_batch = (uint32_t)o->batch_size;
+  lim.max_bytes_per_batch = cap_bytes;
+  lim.max_read_len = (max_line + 63u) & ~63u;
+  lim.n_slots = HQ_SLOTS;
+  lim.host_staging = 1;
+  lim.kmers = (uint32_t)(o->command == HQ_CMD_STATS && o->kmers_on);
+  lim.k2 = lim.kmers ? (uint32_t)o->k2 : 0;
+  lim.cg_k = o->command == HQ_CMD_STATS ? (uint32_t)o->cg_k : 0;
+  for (int g = 0; g < r->n_gpus; g++) {
+    if ((rc = hpgq_ctx_create(g, &lim, &r->ctx[g]))) {
+      die_hpgq("hpgq_ctx_create", rc);
+      goto out;
+    }
+    if ((rc = hpgq_set_params(r->ctx[g], &par))) {
+      die_hpgq("hpgq_set_params", rc);
+      goto out;
+    }
+    for (int s = 0; s < HQ_SLOTS; s++)
+      if ((rc = alloc_host_batch(&r->hb[g][s], lim.max_reads_per_batch, cap_bytes))) {
+        die_hpgq("pinned batch allocation", rc);
+        goto out;
+      }
+  }
+  if (o->command == HQ_CMD_FILTER) {
+    snprintf(pass_name, sizeof pass_name, "%s/passed.fq", o->out_dirname); /* src/filter_fastq.c:185 */
+    snprintf(fail_name, sizeof fail_name, "%s/failed.fq", o->out_dirname); /* src/filter_fastq.c:189 */
+  } else if (o->command == HQ_CMD_EDIT) {
+    snprintf(pass_name, sizeof pass_name, "%s/edit.fq", o->out_dirname);   /* src/edit_fastq.c:217 */
+    if (o->filter_on) snprintf(fail_name, sizeof fail_name, "%s/failed.fq", o->out_dirname); /* :223 */
+  }
+  if (pass_name[0] && hq_writer_open(pass_name, &r->w_pass)) {
+    fprintf(stderr, "\nFATAL: cannot create %s\n", pass_name);
+    goto out;
+  }
+  if (fail_name[0] && hq_writer_open(fail_name, &r->w_fail)) {
+    fprintf(stderr, "\nFATAL: cannot create %s\n", fail_name);
+    goto out;
+  }
+
+  if (run_pipeline(r)) goto out;
+
+  if (r->w_pass && hq_writer_close(r->w_pass)) {
+    r->w_pass = NULL;
+    fprintf(stderr, "\nFATAL: write error on %s\n", pass_name);
+    goto out;
+  }
+  r->w_pass = NULL;
+  if (r->w_fail && hq_writer_close(r->w_fail)) {
+    r->w_fail = NULL;
+    fprintf(stderr, "\nFATAL: write error on %s\n", fail_name);
+    goto out;
+  }
+  r->w_fail = NULL;
+
+  if (o->command == HQ_CMD_STATS) {
+    /* end of run: one sum-allreduce of the counter blocks, one download, then stats_report() */
+    if ((rc = hpgq_counters_reduce(r->ctx, r->n_gpus))) {
+      die_hpgq("hpgq_counters_reduce", rc);
+      goto out;
+    }
+    hpgq_layout_t lay;
+    hpgq_get_layout(r->ctx[0], &lay);
+    const size_t words = lay.offset[HPGQ_SEC_COUNT];
+    uint64_t *blk = (uint64_t *)malloc(words * sizeof(uint64_t));
+    if (!blk) goto out;
+    if ((rc = hpgq_counters_download(r->ctx[0], blk, words))) {
+      free(blk);
+      die_hpgq("hpgq_counters_download", rc);
+      goto out;
+    }
+    if (hq_stats_report(&lay, blk, o)) {
+      free(blk);
+      fprintf(stderr, "\nFATAL: cannot write the report files into %s\n", o->out_dirname);
+      goto out;
+    }
+    /* RESULTS block, src/stats_fastq.c:486-498 */
+    printf("\n\n");
+    printf("RESULTS\n");
+    printf("=================================================\n");
+    printf("Report files and images were stored in '%s' directory\n", o->out_dirname);
+    if (o->filter_on) {
+      printf("\nFiltering: enabled\n");
+      printf("\tSo, statistics were computed for %lu of %lu reads.\n", (unsigned long)blk[HPGQ_S_NUM_PASSED],
+             (unsigned long)(blk[HPGQ_S_NUM_PASSED] + blk[HPGQ_S_NUM_FAILED]));
+    } else {
+      printf("\nFiltering: disabled\n");
+      printf("\tSo, statistics were computed for the whole input file.\n");
+    }
+    printf("=================================================\n");
+    free(blk);
+  } else if (o->command == HQ_CMD_FILTER) {
+    /* src/filter_fastq.c:226-231 */
+    printf("\n\n");
+    printf("RESULTS\n");
+    printf("=================================================\n");
+    printf("Num. passed reads: %lu (%s)\n", (unsigned long)r->num_passed, pass_name);
+    printf("Num. failed reads: %lu (%s)\n", (unsigned long)r->num_failed, fail_name);
+    printf("=================================================\n");
+  } else {
+    /* src/edit_fastq.c:262-272 */
+    printf("\n\n");
+    printf("RESULTS\n");
+    printf("=================================================\n");
+    printf("Num. edited reads : %lu\n", (unsigned long)r->num_edited);
+    printf("Output file       : %s\n", pass_name);
+    if (o->filter_on) {
+      printf("\nFiltering : Enabled\n");
+      printf("\tNum. passed reads : %lu (%s)\n", (unsigned long)r->num_passed, pass_name);
+      printf("\tNum. failed reads : %lu (%s)\n", (unsigned long)r->num_failed, fail_name);
+    }
+    printf("=================================================\n");
+  }
+  {
+    char msg[256];
+    const double dt = now_s() - t0;
+    snprintf(msg, sizeof msg, "%s: %lu reads on %d GPU(s) in %.3f s (%.3g reads/s, %s)", o->command_name,
+             (unsigned long)r->num_reads, r->n_gpus, dt, dt > 0 ? (double)r->num_reads / dt : 0.0, hpgq_version());
+    logf_("INFO", msg);
+  }
+  status = 0;
+out:
+  if (r->w_pass) hq_writer_close(r->w_pass);
+  if (r->w_fail) hq_writer_close(r->w_fail);
+  for (int g = 0; g < HQ_MAX_GPUS; g++) {
+    if (r->ctx[g]) hpgq_ctx_destroy(r->ctx[g]);
+    for (int s = 0; s < HQ_SLOTS; s++) free_host_batch(&r->hb[g][s]);
+  }
+  if (r->reader) hq_reader_close(r->reader);
+  free(r);
+  return status;
+}
+
+int main(int argc, char *argv[]) {
+  const char *exec_name = argv[0];
+  if (argc == 1 || !strcmp(argv[1], "-h") || !strcmp(argv[1], "--help")) {
+    usage(exec_name);
+    return 255; /* the reference exits with -1 here, src/hpg-fastq.c:30 */
+  }
+  const char *command_name = argv[1];
+  if (strcmp(command_name, "stats") && strcmp(command_name, "filter") && strcmp(command_name, "edit")) {
+    usage(exec_name);
+    return 255;
+  }
+  hq_options_t *o = hq_options_parse(exec_name, command_name, argc - 1, argv + 1);
+  if (!o) return 255;
+  if (!hq_options_validate(o)) {
+    hq_options_free(o);
+    return 255;
+  }
+  if (!hq_options_display(o, stdout)) {
+    hq_options_free(o);
+    return 255;
+  }
+  g_log = fopen("hpg-fastq.log", "w"); /* init_log_custom(..., "hpg-fastq.log", "w"), src/hpg-fastq.c:66 */
+  int rc = run_command(o);
+  if (!rc) logf_("INFO", "Done !");
+  if (g_log) fclose(g_log);
+  hq_options_free(o);
+  return rc ? 1 : 0;
+}

@@ -209,6 +209,11 @@ int hpgq_counters_reset(hpgq_ctx_t *ctx);
 int hpgq_counters_download(hpgq_ctx_t *ctx, uint64_t *dst, size_t n_words);
 /* Device pointer of the flat block, for an external sum-allreduce (NCCL / torch.distributed). */
 int hpgq_counters_device_ptr(hpgq_ctx_t *ctx, uint64_t **dptr, size_t *n_words);
+/* Multi-GPU merge: ONE ncclAllReduce(ncclSum, ncclUint64) over the flat blocks of n contexts that
+ * live on n different devices of this process; afterwards every context holds the sum.  Replaces nothing in the
+ * reference (its consumer is a single thread, src/stats_fastq.c:257-417); NCCL is bound with dlopen at the
+ * first call.  n == 1 is a no-op. */
+int hpgq_counters_reduce(hpgq_ctx_t **ctxs, int n);
 /* Fill the derived scalars (totals, min/max length) of a host copy, e.g. after an allreduce. */
 int hpgq_counters_finalize_host(const hpgq_layout_t *layout, uint64_t *block);
 

@@ -1,0 +1,169 @@
+"""GPU tests of the `hpg-fastq` program (C host over the C ABI): the report files, passed/failed/edit FASTQ files
+and RESULTS blocks of `stats`, `filter` and `edit` against the CPU oracle + the Python restatement of
+src/stats_report.c, byte for byte, on a synthetic FASTQ file."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import host_binding as hb
+import report_oracle as ro
+
+pytestmark = pytest.mark.gpu
+
+N_READS = 30000
+
+
+@pytest.fixture(scope="module")
+def fastq(q, tmp_path_factory):
+    d = tmp_path_factory.mktemp("cli")
+    cfg = q.synth_cfg((35, 150), seed=2024)
+    seq, qual, idx = q.synth_host(cfg, 0, N_READS)
+    hdr = [b"@SYN." + str(i).encode() + b" " + str(i).encode() + b"/1" for i in range(N_READS)]
+    path = str(d / "reads.fq")
+    hb.write_fastq(path, hdr, seq, qual, idx)
+    return dict(dir=d, path=path, seq=seq, qual=qual, idx=idx, hdr=hdr)
+
+
+def run_cli(fastq, command, args, sub):
+    out = fastq["dir"] / sub
+    out.mkdir(exist_ok=True)
+    r = subprocess.run([hb.CLI, command, "-f", fastq["path"], "-o", str(out)] + args, capture_output=True, text=True,
+                       cwd=str(out), timeout=600)
+    assert r.returncode == 0, f"{command} {args}: rc={r.returncode}\n{r.stdout[-2000:]}\n{r.stderr[-2000:]}"
+    assert (out / "hpg-fastq.log").exists()
+    return out, r.stdout
+
+
+def oracle_for(q, ob, fastq, command, args, Lcap=192):
+    o = hb.Options(command, ["-f", fastq["path"]] + args)
+    assert o.valid and o.runnable
+    par = o.params(q.Params)
+    if command == "stats" and (par.work & q.WORK_FILTER):
+        hb.lib().hq_options_fill_unset(o.ptr)
+        par = o.params(q.Params)
+    o.close()
+    kmers = bool(par.work & q.WORK_KMERS)
+    lay = ob.layout(q.Layout, Lcap, kmers=int(kmers), k2=par.k2 if kmers else 0, cg_k=par.cg_k)
+    blk, mask, trim = ob.process_batch(par, lay, fastq["seq"], fastq["qual"], fastq["idx"])
+    return par, lay, blk, mask, trim
+
+
+def arg_opts(args):
+    opts = {}
+    for k in ("read-length-range", "read-quality-range", "left-quality-range", "right-quality-range"):
+        if "--" + k in args:
+            opts[k.replace("-", "_")] = args[args.index("--" + k) + 1]
+    for k in ("left-length", "right-length", "max-N", "max-out-of-quality"):
+        if "--" + k in args:
+            opts[k.replace("-", "_")] = int(args[args.index("--" + k) + 1])
+    return opts
+
+
+STATS_CASES = [
+    ("plain", []),
+    ("kmers_small_batches", ["--kmers", "--batch-size", "1000"]),
+    ("filter", ["--read-length-range", "50,", "--read-quality-range", "20,", "--max-N", "5"]),
+    ("filter_windows", ["--read-length-range", "40,140", "--read-quality-range", "18,40", "--max-out-of-quality", "30",
+                        "--left-length", "10", "--left-quality-range", "20,", "--right-length", "12",
+                        "--right-quality-range", "15,45", "--kmers", "--batch-size", "7777"]),
+]
+
+
+@pytest.mark.parametrize("name,args", STATS_CASES, ids=[c[0] for c in STATS_CASES])
+def test_stats_report_files(q, ob, fastq, name, args):
+    out, stdout = run_cli(fastq, "stats", args, "stats_" + name)
+    par, lay, blk, mask, _ = oracle_for(q, ob, fastq, "stats", args)
+    filter_on = bool(par.work & q.WORK_FILTER)
+    rep = ro.Report(lay, blk, "reads.fq", kmers_on="--kmers" in args, filter_on=filter_on, opts=arg_opts(args))
+    exp = rep.files()
+    got = {p.name: p.read_text() for p in out.iterdir() if p.name.startswith("reads.fq.") and not p.name.endswith(".gnuplot")}
+    assert sorted(got) == sorted(exp)
+    for k in exp:
+        assert got[k] == exp[k], f"{k} differs from the restated reference report"
+    if filter_on:
+        npass = int(mask.sum())
+        assert f"\tSo, statistics were computed for {npass} of {N_READS} reads.\n" in stdout
+        assert 0 < npass < N_READS
+    else:
+        assert "Filtering: disabled" in stdout
+
+
+def test_stats_extensions_k11_and_chaos(q, ob, fastq):
+    """--kmers2 11 / --chaos-game 7: tables in the extension files equal the oracle's sections."""
+    args = ["--kmers", "--kmers2", "11", "--chaos-game", "7"]
+    out, _ = run_cli(fastq, "stats", args, "stats_ext")
+    par, lay, blk, _, _ = oracle_for(q, ob, fastq, "stats", args)
+    k2 = lay.section(blk, "K2")
+    lines = (out / "reads.fq.kmers.k11.txt").read_text().splitlines()[1:]
+    got = {l.split("\t")[0]: int(l.split("\t")[1]) for l in lines}
+    nz = np.nonzero(k2)[0]
+    assert len(got) == len(nz)
+    for i in nz[:: max(1, len(nz) // 500)]:
+        assert got[ro.kmer_string(int(i), 11)] == int(k2[i])
+    assert sum(got.values()) == int(k2.sum())
+    freq = np.loadtxt(out / "reads.fq.chaos.k7.freq.data", dtype=np.uint64)
+    qual = np.loadtxt(out / "reads.fq.chaos.k7.quality.data", dtype=np.uint64)
+    assert np.array_equal(freq.reshape(-1), lay.section(blk, "CG_SEQ")[:128 * 128])
+    assert np.array_equal(qual.reshape(-1), lay.section(blk, "CG_Q")[:128 * 128])
+
+
+FILTER_ARGS = ["--read-length-range", "50,", "--read-quality-range", "20,", "--max-N", "5"]
+
+
+@pytest.mark.parametrize("extra", [[], ["--batch-size", "999"]], ids=["one_batch", "many_batches"])
+def test_filter_outputs(q, ob, fastq, extra):
+    out, stdout = run_cli(fastq, "filter", FILTER_ARGS + extra, "filter_" + str(len(extra)))
+    _, _, _, mask, _ = oracle_for(q, ob, fastq, "filter", FILTER_ARGS)
+    passed = np.nonzero(mask)[0].tolist()
+    failed = np.nonzero(mask == 0)[0].tolist()
+    assert passed and failed
+    f = fastq
+    assert (out / "passed.fq").read_bytes() == ro.fastq_text(f["hdr"], f["seq"], f["qual"], f["idx"], order=passed)
+    assert (out / "failed.fq").read_bytes() == ro.fastq_text(f["hdr"], f["seq"], f["qual"], f["idx"], order=failed)
+    assert f"Num. passed reads: {len(passed)} ({out}/passed.fq)\n" in stdout
+    assert f"Num. failed reads: {len(failed)} ({out}/failed.fq)\n" in stdout
+
+
+EDIT_ARGS = ["--left-length", "10", "--left-quality-range", "34,", "--right-length", "10", "--right-quality-range", "22,"]
+
+
+@pytest.mark.parametrize("filt", [[], FILTER_ARGS + ["--batch-size", "4096"]], ids=["edit_only", "edit_filter"])
+def test_edit_outputs(q, ob, fastq, filt):
+    out, stdout = run_cli(fastq, "edit", EDIT_ARGS + filt, "edit_" + str(len(filt)))
+    par, _, blk, mask, trim = oracle_for(q, ob, fastq, "edit", EDIT_ARGS + filt)
+    f = fastq
+    lens = np.diff(f["idx"].astype(np.int64))
+    n_edited = int((trim[:, 1] != lens).sum())
+    assert 0 < n_edited < N_READS
+    assert f"Num. edited reads : {n_edited}\n" in stdout
+    if filt:
+        passed = np.nonzero(mask)[0].tolist()
+        failed = np.nonzero(mask == 0)[0].tolist()
+        assert passed and failed
+        assert (out / "edit.fq").read_bytes() == ro.fastq_text(f["hdr"], f["seq"], f["qual"], f["idx"], order=passed, trim=trim)
+        assert (out / "failed.fq").read_bytes() == ro.fastq_text(f["hdr"], f["seq"], f["qual"], f["idx"], order=failed, trim=trim)
+        assert f"\tNum. passed reads : {len(passed)} ({out}/edit.fq)\n" in stdout
+    else:
+        assert (out / "edit.fq").read_bytes() == ro.fastq_text(f["hdr"], f["seq"], f["qual"], f["idx"], trim=trim)
+        assert not (out / "failed.fq").exists()
+
+
+def test_multi_gpu_round_robin_same_files(q, ob, fastq):
+    """--gpus 2: batches dealt round-robin, counters merged by one NCCL allreduce, outputs in input order."""
+    n = C.c_int(0)
+    q.load_library().hpgq_device_count(C.byref(n))
+    if n.value < 2:
+        pytest.skip("needs 2 GPUs")
+    args = ["--kmers", "--batch-size", "1500", "--read-quality-range", "20,"]
+    one, _ = run_cli(fastq, "stats", args, "mg_stats1")
+    two, _ = run_cli(fastq, "stats", args + ["--gpus", "2"], "mg_stats2")
+    for p in one.iterdir():
+        if p.name.startswith("reads.fq.") and not p.name.endswith(".gnuplot"):
+            assert (two / p.name).read_bytes() == p.read_bytes(), p.name
+    f1, _ = run_cli(fastq, "filter", FILTER_ARGS + ["--batch-size", "1500"], "mg_f1")
+    f2, _ = run_cli(fastq, "filter", FILTER_ARGS + ["--batch-size", "1500", "--gpus", "2"], "mg_f2")
+    assert (f1 / "passed.fq").read_bytes() == (f2 / "passed.fq").read_bytes()
+    assert (f1 / "failed.fq").read_bytes() == (f2 / "failed.fq").read_bytes()
