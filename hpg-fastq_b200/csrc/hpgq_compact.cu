@@ -111,37 +111,97 @@ __global__ void __launch_bounds__(SCAN_THREADS) hq_compact_scan(hq_kargs a, cons
   }
 }
 
-// pass 4: copy. One warp per read; output slot and byte offset come from the scan.
+// pass 4: copy.  G lanes per read; a lane moves DESTINATION-aligned 16-byte chunks.  The source of such a chunk
+// starts at an arbitrary byte, always with the same phase inside a read, so every lane loads ONE aligned 16-byte
+// source chunk per array, takes the following one from its neighbour lane by shuffle, and funnel-shifts the pair
+// into the 16 bytes it stores.  The partial chunks at the two ends of a read are moved byte by byte.
+__device__ __forceinline__ uint4 shift_pair(const uint4 &A, const uint4 &B, uint32_t sh) {
+  // bytes [sh, sh + 16) of the 32 bytes A:B
+  const uint32_t bs = (sh & 3u) * 8u;
+  uint32_t w0, w1, w2, w3, w4;
+  switch (sh >> 2) {
+    case 0: w0 = A.x; w1 = A.y; w2 = A.z; w3 = A.w; w4 = B.x; break;
+    case 1: w0 = A.y; w1 = A.z; w2 = A.w; w3 = B.x; w4 = B.y; break;
+    case 2: w0 = A.z; w1 = A.w; w2 = B.x; w3 = B.y; w4 = B.z; break;
+    default: w0 = A.w; w1 = B.x; w2 = B.y; w3 = B.z; w4 = B.w; break;
+  }
+  return make_uint4(__funnelshift_r(w0, w1, bs), __funnelshift_r(w1, w2, bs), __funnelshift_r(w2, w3, bs),
+                    __funnelshift_r(w3, w4, bs));
+}
+
+__device__ __forceinline__ uint4 shfl_down4(const uint4 &v, unsigned gmask) {
+  return make_uint4(__shfl_down_sync(gmask, v.x, 1), __shfl_down_sync(gmask, v.y, 1), __shfl_down_sync(gmask, v.z, 1),
+                    __shfl_down_sync(gmask, v.w, 1));
+}
+
+template <int G>
 __global__ void __launch_bounds__(256) hq_compact_copy(hq_kargs a, hq_compact_bufs b) {
-  const uint32_t lane = threadIdx.x & 31u;
-  const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
+  const uint32_t gtid = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t lig = gtid % G, grp = gtid / G, ngrp = (gridDim.x * blockDim.x) / G;
+  const unsigned gmask = (G == 32 ? 0xFFFFFFFFu : ((1u << G) - 1u)) << ((threadIdx.x & 31u) / G * G);
   const uint32_t n = a.n_reads;
   const uint4 tot = b.scan[n];
-  for (uint32_t i = warp; i < n; i += nwarps) {
+  for (uint32_t i = grp; i < n; i += ngrp) {  // group-uniform loop: shuffles below name the group's lanes only
     const uint4 sc = b.scan[i];
     const bool pass = a.mask ? (a.mask[i] != 0) : true;
     const uint32_t st = a.trim ? a.trim[i].start : 0u;
     const uint32_t ln = a.trim ? a.trim[i].len : (a.idx[i + 1] - a.idx[i]);
     const uint32_t dst = pass ? sc.x : tot.x + sc.y;
     const uint32_t slot = pass ? sc.z : tot.z + sc.w;
-    if (lane == 0) {
+    if (lig == 0) {
       b.out_src[slot] = i;
       b.out_idx[slot] = dst;
     }
-    const uint8_t *s = a.seq + a.idx[i] + st, *q = a.qual + a.idx[i] + st;
-    uint8_t *ds = b.out_seq + dst, *dq = b.out_qual + dst;
-    for (uint32_t j = lane; j < ln; j += 32) {
-      ds[j] = s[j];
-      dq[j] = q[j];
+    if (ln == 0) continue;
+    const uint32_t so = a.idx[i] + st;
+    const uint32_t db = dst & ~15u, de = dst + ln;
+    const uint32_t nch = (de - db + 15u) >> 4;
+    const uint32_t sh = (so - dst) & 15u;  // byte phase of the source inside its aligned chunk, same for all chunks
+    for (uint32_t k0 = 0; k0 < nch; k0 += G) {
+      const uint32_t k = k0 + lig;
+      const uint32_t dc = db + 16u * k;
+      const bool head = k < nch && dc < dst;                     // first chunk, starts before the read
+      const bool full = k < nch && !head && de - dc >= 16u;
+      // valid destination bytes of the chunk and the source byte that lands on the first of them
+      const uint32_t lo = head ? dst : dc, hi = (k < nch && de - dc >= 16u) ? dc + 16u : de;
+      const uint32_t sa = so + (lo - dst);
+      const bool ld = k <= nch;  // chunk nch only feeds the B half of chunk nch-1
+      uint4 As = make_uint4(0, 0, 0, 0), Aq = As;
+      if (ld) {
+        As = __ldg(reinterpret_cast<const uint4 *>(a.seq + (sa & ~15u)));
+        Aq = __ldg(reinterpret_cast<const uint4 *>(a.qual + (sa & ~15u)));
+      }
+      uint4 Bs = shfl_down4(As, gmask), Bq = shfl_down4(Aq, gmask);
+      // the head chunk has its own source phase, and the last lane's neighbour belongs to the next round
+      if ((head || lig == G - 1) && k < nch && (sa & 15u)) {
+        Bs = __ldg(reinterpret_cast<const uint4 *>(a.seq + (sa & ~15u) + 16u));
+        Bq = __ldg(reinterpret_cast<const uint4 *>(a.qual + (sa & ~15u) + 16u));
+      }
+      if (k < nch) {
+        const uint4 vs = shift_pair(As, Bs, sa & 15u), vq = shift_pair(Aq, Bq, sa & 15u);
+        if (full) {
+          *reinterpret_cast<uint4 *>(b.out_seq + dc) = vs;
+          *reinterpret_cast<uint4 *>(b.out_qual + dc) = vq;
+        } else {  // partial chunk: the bytes are in registers, predicated byte stores
+          const uint32_t cnt = hi - lo;
+          const uint32_t ws[4] = {vs.x, vs.y, vs.z, vs.w}, wq[4] = {vq.x, vq.y, vq.z, vq.w};
+#pragma unroll
+          for (int t = 0; t < 15; ++t)
+            if ((uint32_t)t < cnt) {
+              b.out_seq[lo + t] = (uint8_t)(ws[t >> 2] >> (8 * (t & 3)));
+              b.out_qual[lo + t] = (uint8_t)(wq[t >> 2] >> (8 * (t & 3)));
+            }
+        }
+      }
     }
   }
-  if (warp == 0 && lane == 0) b.out_idx[n] = tot.x + tot.y;
+  if (gtid == 0) b.out_idx[n] = tot.x + tot.y;
 }
 
 } // namespace
 
-cudaError_t hq_launch_compact(const hq_kargs &a, const hq_compact_bufs &b, cudaStream_t st, uint64_t *launches) {
+cudaError_t hq_launch_compact(const hq_kargs &a, const hq_compact_bufs &b, uint32_t mean_len, cudaStream_t st,
+                              uint64_t *launches) {
   const uint32_t n1 = a.n_reads + 1u;
   const uint32_t nb = (n1 + SCAN_THREADS * SCAN_ITEMS - 1u) / (SCAN_THREADS * SCAN_ITEMS);
   hq_compact_sums<<<nb, SCAN_THREADS, 0, st>>>(a, b.block_sums);
@@ -149,9 +209,15 @@ cudaError_t hq_launch_compact(const hq_kargs &a, const hq_compact_bufs &b, cudaS
   hq_compact_scan<<<nb, SCAN_THREADS, 0, st>>>(a, b.block_sums, b.scan, b.totals);
   *launches += 3;
   if (a.n_reads) {
-    uint32_t blocks = (a.n_reads + 7u) / 8u;
-    if (blocks > 148u * 16u) blocks = 148u * 16u;
-    hq_compact_copy<<<blocks, 256, 0, st>>>(a, b);
+    // lanes per read from the mean read length of the batch (bytes / reads are known to the caller only as
+    // capacities, so use the idx span): short reads take 8 or 16 lanes, long reads a whole warp
+    const int G = mean_len <= 112u ? 8 : mean_len <= 400u ? 16 : 32;
+    const uint32_t rpb = 256u / (uint32_t)G;
+    uint32_t blocks = (a.n_reads + rpb - 1u) / rpb;
+    if (blocks > 148u * 32u) blocks = 148u * 32u;
+    if (G == 8) hq_compact_copy<8><<<blocks, 256, 0, st>>>(a, b);
+    else if (G == 16) hq_compact_copy<16><<<blocks, 256, 0, st>>>(a, b);
+    else hq_compact_copy<32><<<blocks, 256, 0, st>>>(a, b);
     ++*launches;
   }
   return cudaGetLastError();

@@ -28,15 +28,15 @@ HQ_HDI uint32_t hq_prmt(uint32_t a, uint32_t b, uint32_t s) {
 #endif
 }
 
-// PRMT without the (s & 0x7777) that __byte_perm's contract forces the compiler to emit: only for
-// selectors whose nibbles are known to be <= 7 (bits above 15 are ignored by the instruction)
+// Raw PTX prmt (default mode): no (s & 0x7777) as __byte_perm's contract forces the compiler to emit, and a
+// selector nibble with its msb set replicates the sign bit of the selected byte (bits above 15 are ignored)
 HQ_HDI uint32_t hq_prmt_raw(uint32_t a, uint32_t b, uint32_t s) {
 #ifdef __CUDA_ARCH__
   uint32_t r;
   asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(s));
   return r;
 #else
-  return hq_prmt(a, b, s & 0x7777u);
+  return hq_prmt(a, b, s);
 #endif
 }
 

@@ -1,0 +1,556 @@
+// hpgq_group.cu -- vectorised QC kernels for everything the tiled kernel does not take: reads of ANY length
+// (long-read config C5) and the EDIT path (config C3).
+//
+//   hq_qc_group_kernel<G>   G lanes own one read; 16-byte coalesced loads of the quality / sequence bytes, SIMD-in-word
+//                           sums, shuffle reduction inside the group.  Computes the trim decision (fastq_edit,
+//                           reference call src/edit_fastq.c:148-154), the pass/fail decision (fastq_filter,
+//                           src/stats_fastq.c:209-224) and the per-read part of the consumer merge (length / mean
+//                           quality / GC histograms, src/stats_fastq.c:286-334).
+//   hq_pos_kernel           per-position part of the merge (src/stats_fastq.c:338-382) for long reads: a thread OWNS
+//                           eight read positions and walks over the reads of its slab, so the A/C/G/T/N and quality
+//                           sums are register accumulators -- no atomics in the loop; the grid is
+//                           (position tiles) x (read slabs).
+// Both read HBM with full 128-byte-and-wider warp requests; the second kernel re-reads the batch (2 passes).
+#include "hpgq_dev.cuh"
+#include "hpgq_internal.h"
+
+namespace {
+
+struct hq_sums4 {
+  uint32_t S, nN, nGC, ooq;
+};
+
+__device__ __forceinline__ bool mean_ok_g(uint32_t S, uint32_t w, int32_t lo, int32_t hi) {
+  const long long s = (long long)S, ww = (long long)w;
+  return s >= (long long)lo * ww && s <= (long long)hi * ww;
+}
+
+template <bool SEQ>
+__device__ __forceinline__ void acc_word(const hq_kargs &a, uint32_t qw, uint32_t sw, uint32_t m, hq_sums4 &r) {
+  const uint32_t qm = qw & m;
+  r.S = __dp4a(qm, 0x01010101u, r.S);
+  if (SEQ) {
+    if (qm & 0x80808080u) {  // bytes >= 128 are not ASCII qualities: exact per-byte comparison
+      for (int i = 0; i < 4; ++i)
+        if ((m >> (8 * i)) & 1u) {
+          const int32_t qq = (int32_t)((qw >> (8 * i)) & 0xFFu);
+          r.ooq += (qq < a.q_lo) | (qq > a.q_hi);
+        }
+    } else {
+      r.ooq += hq_ooq_count(qw, m, a.c_lo, a.c_hi);
+    }
+    r.nN += __popc(__vcmpeq4(sw, 0x4E4E4E4Eu) & m & 0x01010101u);
+    r.nGC += __popc((__vcmpeq4(sw, 0x47474747u) | __vcmpeq4(sw, 0x43434343u)) & m & 0x01010101u);
+  }
+}
+
+// sums over the bytes [lo, hi) (offsets into the batch arrays) by the G lanes of a group, NOT yet reduced
+template <int G, bool SEQ>
+__device__ __forceinline__ hq_sums4 range_sums(const hq_kargs &a, uint32_t lo, uint32_t hi, uint32_t lig) {
+  hq_sums4 r = {0u, 0u, 0u, 0u};
+  if (hi <= lo) return r;
+  const uint32_t base = lo & ~15u;
+  const uint32_t nch = (hi - base + 15u) >> 4;
+#pragma unroll 2
+  for (uint32_t k = lig; k < nch; k += G) {
+    const uint32_t c = base + 16u * k;
+    const uint4 q = *reinterpret_cast<const uint4 *>(a.qual + c);
+    uint4 s = make_uint4(0, 0, 0, 0);
+    if (SEQ) s = *reinterpret_cast<const uint4 *>(a.seq + c);
+    if (c >= lo && hi - c >= 16u) {
+      acc_word<SEQ>(a, q.x, s.x, 0xFFFFFFFFu, r);
+      acc_word<SEQ>(a, q.y, s.y, 0xFFFFFFFFu, r);
+      acc_word<SEQ>(a, q.z, s.z, 0xFFFFFFFFu, r);
+      acc_word<SEQ>(a, q.w, s.w, 0xFFFFFFFFu, r);
+    } else {
+      acc_word<SEQ>(a, q.x, s.x, hq_tail_mask(c, hi) & ~hq_tail_mask(c, lo), r);
+      acc_word<SEQ>(a, q.y, s.y, hq_tail_mask(c + 4u, hi) & ~hq_tail_mask(c + 4u, lo), r);
+      acc_word<SEQ>(a, q.z, s.z, hq_tail_mask(c + 8u, hi) & ~hq_tail_mask(c + 8u, lo), r);
+      acc_word<SEQ>(a, q.w, s.w, hq_tail_mask(c + 12u, hi) & ~hq_tail_mask(c + 12u, lo), r);
+    }
+  }
+  return r;
+}
+
+template <int G>
+__device__ __forceinline__ uint32_t group_sum(uint32_t v) {
+#pragma unroll
+  for (int o = G / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o);
+  return v;
+}
+
+template <int G>
+__global__ void __launch_bounds__(256) hq_qc_group_kernel(hq_kargs a) {
+  constexpr uint32_t NG = 32u / G;  // groups per warp
+  const uint32_t lane = threadIdx.x & 31u, lig = lane % G, giw = lane / G;
+  const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
+  const bool do_stats = a.work & HPGQ_WORK_STATS, do_filter = a.work & HPGQ_WORK_FILTER;
+  const bool do_edit = a.work & HPGQ_WORK_EDIT;
+  unsigned long long *C = a.ctr;
+  uint32_t n_pass = 0, n_fail = 0, n_edit = 0, n_stat = 0;
+  unsigned long long acc_len = 0;
+
+  // warp-uniform trip count: every lane reaches every shuffle
+  for (uint32_t r0 = warp * NG; r0 < a.n_reads; r0 += nwarps * NG) {
+    const uint32_t r = r0 + giw;
+    const bool live = r < a.n_reads;
+    const uint32_t o = live ? a.idx[r] : 0u;
+    const uint32_t L0 = live ? a.idx[r + 1] - o : 0u;
+    uint32_t start = 0, len = L0;
+    if (do_edit) {
+      bool edited = false;
+      if (a.e_ll > 0) {
+        const uint32_t w = min((uint32_t)a.e_ll, len);
+        const uint32_t sw = group_sum<G>(range_sums<G, false>(a, o, o + w, lig).S);
+        if (w && !mean_ok_g(sw, w, a.e_lq_lo, a.e_lq_hi)) {
+          start += w;
+          len -= w;
+          edited = true;
+        }
+      }
+      if (a.e_rl > 0) {
+        const uint32_t w = min((uint32_t)a.e_rl, len);
+        const uint32_t e = o + start + len;
+        const uint32_t sw = group_sum<G>(range_sums<G, false>(a, e - w, e, lig).S);
+        if (w && !mean_ok_g(sw, w, a.e_rq_lo, a.e_rq_hi)) {
+          len -= w;
+          edited = true;
+        }
+      }
+      n_edit += (edited && lig == 0);
+    }
+    if (a.trim && live && lig == 0) a.trim[r] = hpgq_trim_t{start, len};
+    const uint32_t b0 = o + start, b1 = b0 + len;
+    hq_sums4 t = range_sums<G, true>(a, b0, b1, lig);
+    t.S = group_sum<G>(t.S);
+    t.nN = group_sum<G>(t.nN);
+    t.nGC = group_sum<G>(t.nGC);
+    bool pass = true;
+    if (do_filter) {
+      t.ooq = group_sum<G>(t.ooq);
+      const uint32_t wl = a.f_ll > 0 ? min((uint32_t)a.f_ll, len) : 0u;
+      const uint32_t wr = a.f_rl > 0 ? min((uint32_t)a.f_rl, len) : 0u;
+      pass = (long long)len >= a.min_len && (long long)len <= a.max_len && mean_ok_g(t.S, len, a.q_lo, a.q_hi) &&
+             (long long)t.ooq <= a.max_ooq && (long long)t.nN <= a.max_n;
+      if (a.f_ll > 0) {
+        const uint32_t SL = group_sum<G>(range_sums<G, false>(a, b0, b0 + wl, lig).S);
+        if (wl) pass = pass && mean_ok_g(SL, wl, a.f_lq_lo, a.f_lq_hi);
+      }
+      if (a.f_rl > 0) {
+        const uint32_t SR = group_sum<G>(range_sums<G, false>(a, b1 - wr, b1, lig).S);
+        if (wr) pass = pass && mean_ok_g(SR, wr, a.f_rq_lo, a.f_rq_hi);
+      }
+      if (live && lig == 0) {
+        n_pass += pass;
+        n_fail += !pass;
+      }
+    }
+    if (live && lig == 0) {
+      if (a.mask) a.mask[r] = pass ? 1 : 0;
+      if (do_stats && pass && len <= a.Lcap) {
+        n_stat++;
+        acc_len += len;
+        atomicAdd(&C[a.o_len_hist + len], 1ull);
+        atomicAdd(&C[a.o_sumq + len], (unsigned long long)t.S);
+        if (len) {
+          atomicAdd(&C[a.o_qual_hist + (uint32_t)((2ull * t.S + len) / (2ull * len))], 1ull);
+          atomicAdd(&C[a.o_gc_hist + (uint32_t)((100ull * t.nGC) / len)], 1ull);
+        }
+      }
+    }
+  }
+  // one set of scalar atomics per warp
+  n_pass = group_sum<32>(n_pass);
+  n_fail = group_sum<32>(n_fail);
+  n_edit = group_sum<32>(n_edit);
+  n_stat = group_sum<32>(n_stat);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc_len += __shfl_xor_sync(0xFFFFFFFFu, acc_len, o);
+  if (lane == 0) {
+    if (n_pass) atomicAdd(&C[HPGQ_S_NUM_PASSED], (unsigned long long)n_pass);
+    if (n_fail) atomicAdd(&C[HPGQ_S_NUM_FAILED], (unsigned long long)n_fail);
+    if (n_edit) atomicAdd(&C[HPGQ_S_NUM_EDITED], (unsigned long long)n_edit);
+    if (n_stat) atomicAdd(&C[HPGQ_S_NUM_READS], (unsigned long long)n_stat);
+    if (acc_len) atomicAdd(&C[HPGQ_S_ACC_LENGTH], acc_len);
+  }
+}
+
+// ---------------------------------------------------------------- register-resident variant (reads <= 32*G - 15 bytes)
+// The whole read sits in registers: every lane owns 32 consecutive bytes (two 16-byte loads per array).  Bytes
+// outside the read -- and, after the trim decision, outside the kept range -- are ZEROED once, so the main sums
+// run without masks; the few lanes that overlap a quality window build byte masks with SIMD compares.
+constexpr int RG_CPL = 2;            // 16-byte chunks per lane
+constexpr int RG_W = 4 * RG_CPL;     // words per lane
+constexpr int RG_LB = 16 * RG_CPL;   // bytes per lane
+
+// 0xFF in the bytes of word j (byte positions 4j .. 4j+3 of the lane) that lie in [nlo, nhi), 0 <= nlo, nhi <= 32.
+// tlo / thi are nlo / nhi broadcast to the four bytes.
+__device__ __forceinline__ uint32_t rg_mask(int j, uint32_t tlo, uint32_t thi) {
+  const uint32_t P = (0x03020100u + 0x04040404u * (uint32_t)j) | 0x80808080u;
+  const uint32_t f = (P - tlo) & ~(P - thi) & 0x80808080u;  // bit 7: position >= nlo and not >= nhi
+  return hq_prmt_raw(f, 0u, 0xBA98u);                        // PTX prmt, selector msb: replicate each byte's sign bit
+}
+
+// exact 0x80 flag per zero byte of x
+__device__ __forceinline__ uint32_t rg_zero_flags(uint32_t x) {
+  return ~(((x & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | x) & 0x80808080u;
+}
+
+struct rg_read {
+  uint32_t q[RG_W], s[RG_W];
+  uint32_t c;  // batch offset of the lane's first byte
+};
+
+// zero every byte of the lane outside [lo, hi)
+__device__ __forceinline__ void rg_clip(rg_read &d, uint32_t lo, uint32_t hi) {
+  if (d.c >= lo && hi >= d.c + RG_LB) return;  // lane entirely inside
+  const uint32_t nlo = lo > d.c ? min(lo - d.c, (uint32_t)RG_LB) : 0u;
+  const uint32_t nhi = hi > d.c ? min(hi - d.c, (uint32_t)RG_LB) : 0u;
+  const uint32_t tlo = nlo * 0x01010101u, thi = nhi * 0x01010101u;
+#pragma unroll
+  for (int j = 0; j < RG_W; ++j) {
+    const uint32_t m = rg_mask(j, tlo, thi);
+    d.q[j] &= m;
+    d.s[j] &= m;
+  }
+}
+
+// sum of the quality bytes in [lo, hi), this lane's share
+__device__ __forceinline__ uint32_t rg_window_lane(const rg_read &d, uint32_t lo, uint32_t hi) {
+  if (hi <= lo || d.c >= hi || d.c + RG_LB <= lo) return 0u;
+  const uint32_t nlo = lo > d.c ? lo - d.c : 0u;
+  const uint32_t nhi = min(hi - d.c, (uint32_t)RG_LB);
+  const uint32_t tlo = nlo * 0x01010101u, thi = nhi * 0x01010101u;
+  uint32_t S = 0;
+#pragma unroll
+  for (int j = 0; j < RG_W; ++j) S = __dp4a(d.q[j] & rg_mask(j, tlo, thi), 0x01010101u, S);
+  return S;
+}
+
+__device__ __forceinline__ bool mean_ok32(uint32_t S, uint32_t w, int32_t lo, int32_t hi) {
+  return (int32_t)S >= lo * (int32_t)w && (int32_t)S <= hi * (int32_t)w;
+}
+
+template <int G>
+__global__ void __launch_bounds__(256) hq_qc_regs_kernel(hq_kargs a) {
+  constexpr uint32_t NG = 32u / G;
+  constexpr int U = 2;
+  const uint32_t lane = threadIdx.x & 31u, lig = lane % G, giw = lane / G;
+  const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
+  const bool do_stats = a.work & HPGQ_WORK_STATS, do_filter = a.work & HPGQ_WORK_FILTER;
+  const bool do_edit = a.work & HPGQ_WORK_EDIT;
+  const bool zero_is_ooq = a.q_lo > 0 || a.q_hi < 0;  // a zeroed byte counts as out of range: corrected per lane
+  unsigned long long *C = a.ctr;
+  uint32_t n_pass = 0, n_fail = 0, n_edit = 0, n_stat = 0;
+  unsigned long long acc_len = 0;
+
+  for (uint32_t r0 = warp * NG * U; r0 < a.n_reads; r0 += nwarps * NG * U) {
+    uint32_t rr[U], oo[U], LL[U];
+    rg_read d[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      rr[u] = r0 + u * NG + giw;
+      const bool live = rr[u] < a.n_reads;
+      oo[u] = live ? a.idx[rr[u]] : 0u;
+      LL[u] = live ? a.idx[rr[u] + 1] - oo[u] : 0u;
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      d[u].c = (oo[u] & ~15u) + RG_LB * lig;
+#pragma unroll
+      for (int k = 0; k < RG_CPL; ++k) {
+        uint4 q4 = make_uint4(0, 0, 0, 0), s4 = q4;
+        if (d[u].c + 16u * k < oo[u] + LL[u]) {
+          q4 = *reinterpret_cast<const uint4 *>(a.qual + d[u].c + 16u * k);
+          s4 = *reinterpret_cast<const uint4 *>(a.seq + d[u].c + 16u * k);
+        }
+        d[u].q[4 * k + 0] = q4.x; d[u].q[4 * k + 1] = q4.y; d[u].q[4 * k + 2] = q4.z; d[u].q[4 * k + 3] = q4.w;
+        d[u].s[4 * k + 0] = s4.x; d[u].s[4 * k + 1] = s4.y; d[u].s[4 * k + 2] = s4.z; d[u].s[4 * k + 3] = s4.w;
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const uint32_t r = rr[u], o = oo[u];
+      const bool live = r < a.n_reads;
+      uint32_t start = 0, len = LL[u];
+      rg_clip(d[u], o, o + len);
+      if (do_edit) {
+        bool edited = false;
+        if (a.e_ll > 0) {
+          const uint32_t w = min((uint32_t)a.e_ll, len);
+          const uint32_t sw = group_sum<G>(rg_window_lane(d[u], o, o + w));
+          if (w && !mean_ok32(sw, w, a.e_lq_lo, a.e_lq_hi)) {
+            start += w;
+            len -= w;
+            edited = true;
+          }
+        }
+        if (a.e_rl > 0) {
+          const uint32_t w = min((uint32_t)a.e_rl, len);
+          const uint32_t e = o + start + len;
+          const uint32_t sw = group_sum<G>(rg_window_lane(d[u], e - w, e));
+          if (w && !mean_ok32(sw, w, a.e_rq_lo, a.e_rq_hi)) {
+            len -= w;
+            edited = true;
+          }
+        }
+        n_edit += (edited && lig == 0);
+        if (edited) rg_clip(d[u], o + start, o + start + len);
+      }
+      if (a.trim && live && lig == 0) a.trim[r] = hpgq_trim_t{start, len};
+      const uint32_t b0 = o + start, b1 = b0 + len;
+      // main sums over the registers (bytes outside [b0, b1) are zero)
+      uint32_t S = 0, fN = 0, fGC = 0, fO = 0, hib = 0;
+#pragma unroll
+      for (int j = 0; j < RG_W; ++j) {
+        const uint32_t qw = d[u].q[j], sw = d[u].s[j];
+        S = __dp4a(qw, 0x01010101u, S);
+        fN += rg_zero_flags(sw ^ 0x4E4E4E4Eu) >> 7;
+        fGC += rg_zero_flags((sw & 0xFBFBFBFBu) ^ 0x43434343u) >> 7;  // 'C' = 0x43, 'G' = 0x47
+        fO += (~((qw + a.c_lo) & ~(qw + a.c_hi)) & 0x80808080u) >> 7;
+        hib |= qw;
+      }
+      uint32_t nN = __dp4a(fN, 0x01010101u, 0u), nGC = __dp4a(fGC, 0x01010101u, 0u), ooq = __dp4a(fO, 0x01010101u, 0u);
+      if (zero_is_ooq) {  // remove the lane's zeroed bytes from the out-of-range count
+        const uint32_t lo = max(b0, d[u].c), hi = min(b1, d[u].c + RG_LB);
+        ooq -= RG_LB - (hi > lo ? hi - lo : 0u);
+      }
+      if (hib & 0x80808080u) {  // a quality byte >= 128: exact per-byte count for this lane
+        ooq = 0;
+        for (int j = 0; j < RG_W; ++j)
+          for (int i = 0; i < 4; ++i) {
+            const uint32_t pos = d[u].c + 4u * j + i;
+            const int32_t qq = (int32_t)((d[u].q[j] >> (8 * i)) & 0xFFu);
+            if (pos >= b0 && pos < b1) ooq += (qq < a.q_lo) | (qq > a.q_hi);
+          }
+      }
+      // len < 32*G <= 1024: S < 2^18, counts < 2^10 -> two packed shuffle chains
+      uint32_t p1 = S | (nN << 20), p2 = nGC | (ooq << 16);
+      p1 = group_sum<G>(p1);
+      p2 = group_sum<G>(p2);
+      S = p1 & 0xFFFFFu;
+      nN = p1 >> 20;
+      nGC = p2 & 0xFFFFu;
+      ooq = p2 >> 16;
+      bool pass = true;
+      if (do_filter) {
+        pass = (int32_t)len >= a.min_len && (int32_t)len <= a.max_len && mean_ok32(S, len, a.q_lo, a.q_hi) &&
+               (int32_t)ooq <= a.max_ooq && (int32_t)nN <= a.max_n;
+        if (a.f_ll > 0) {
+          const uint32_t wl = min((uint32_t)a.f_ll, len);
+          const uint32_t SL = group_sum<G>(rg_window_lane(d[u], b0, b0 + wl));
+          if (wl) pass = pass && mean_ok32(SL, wl, a.f_lq_lo, a.f_lq_hi);
+        }
+        if (a.f_rl > 0) {
+          const uint32_t wr = min((uint32_t)a.f_rl, len);
+          const uint32_t SR = group_sum<G>(rg_window_lane(d[u], b1 - wr, b1));
+          if (wr) pass = pass && mean_ok32(SR, wr, a.f_rq_lo, a.f_rq_hi);
+        }
+        if (live && lig == 0) {
+          n_pass += pass;
+          n_fail += !pass;
+        }
+      }
+      if (live && lig == 0) {
+        if (a.mask) a.mask[r] = pass ? 1 : 0;
+        if (do_stats && pass && len <= a.Lcap) {
+          n_stat++;
+          acc_len += len;
+          atomicAdd(&C[a.o_len_hist + len], 1ull);
+          atomicAdd(&C[a.o_sumq + len], (unsigned long long)S);
+          if (len) {
+            atomicAdd(&C[a.o_qual_hist + (2u * S + len) / (2u * len)], 1ull);
+            atomicAdd(&C[a.o_gc_hist + (100u * nGC) / len], 1ull);
+          }
+        }
+      }
+    }
+  }
+  n_pass = group_sum<32>(n_pass);
+  n_fail = group_sum<32>(n_fail);
+  n_edit = group_sum<32>(n_edit);
+  n_stat = group_sum<32>(n_stat);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc_len += __shfl_xor_sync(0xFFFFFFFFu, acc_len, o);
+  if (lane == 0) {
+    if (n_pass) atomicAdd(&C[HPGQ_S_NUM_PASSED], (unsigned long long)n_pass);
+    if (n_fail) atomicAdd(&C[HPGQ_S_NUM_FAILED], (unsigned long long)n_fail);
+    if (n_edit) atomicAdd(&C[HPGQ_S_NUM_EDITED], (unsigned long long)n_edit);
+    if (n_stat) atomicAdd(&C[HPGQ_S_NUM_READS], (unsigned long long)n_stat);
+    if (acc_len) atomicAdd(&C[HPGQ_S_ACC_LENGTH], acc_len);
+  }
+}
+
+// ---------------------------------------------------------------- per-position tables, column-owner form
+constexpr int POS_THREADS = 256;
+constexpr int POS_PER = 8;                       // positions owned by a thread (two 32-bit words)
+constexpr int POS_TILE = POS_THREADS * POS_PER;  // positions per CTA
+constexpr int POS_BATCH = 8;                     // reads in flight per thread (memory-level parallelism)
+
+// eight bytes at an arbitrary byte offset: two aligned 8-byte loads and a 64-bit funnel shift
+__device__ __forceinline__ void load8(const uint8_t *base, uint32_t off, uint32_t &v0, uint32_t &v1) {
+  const unsigned long long *w = reinterpret_cast<const unsigned long long *>(base + (off & ~7u));
+  const unsigned long long lo = __ldg(w), hi = __ldg(w + 1);
+  const uint32_t sh = (off & 7u) * 8u;
+  const unsigned long long v = sh ? ((lo >> sh) | (hi << (64u - sh))) : lo;
+  v0 = (uint32_t)v;
+  v1 = (uint32_t)(v >> 32);
+}
+
+// Per-warp queue of the slab's reads that cover this position tile: 32 idx entries are tested per coalesced
+// load, the hits are handed out one by one with shuffles (every warp of the CTA walks the same list).
+struct pos_queue {
+  uint32_t next, end, pend, my_o, my_L;
+};
+
+__device__ __forceinline__ bool pos_pop(const hq_kargs &a, pos_queue &qu, uint32_t p0, bool use_mask, uint32_t lane,
+                                        uint32_t &o, uint32_t &L) {
+  while (qu.pend == 0u) {
+    if (qu.next >= qu.end) return false;
+    const uint32_t r = qu.next + lane;
+    bool ok = false;
+    if (r < qu.end) {
+      qu.my_o = a.idx[r];
+      qu.my_L = a.idx[r + 1] - qu.my_o;
+      ok = qu.my_L > p0 && qu.my_L <= a.Lcap && (!use_mask || a.mask[r]);
+    }
+    qu.pend = __ballot_sync(0xFFFFFFFFu, ok);
+    qu.next += 32u;
+  }
+  const int src = __ffs(qu.pend) - 1;
+  qu.pend &= qu.pend - 1u;
+  o = __shfl_sync(0xFFFFFFFFu, qu.my_o, src);
+  L = __shfl_sync(0xFFFFFFFFu, qu.my_L, src);
+  return true;
+}
+
+__global__ void __launch_bounds__(POS_THREADS, 2) hq_pos_kernel(hq_kargs a, uint32_t reads_per_slab) {
+  // widened sums of the owned positions, [table][position-in-thread][thread]: thread-private cells (no atomics),
+  // kept in shared memory only to leave the registers to the loads in flight
+  __shared__ uint32_t sacc[6 * POS_PER * POS_THREADS];
+  const uint32_t tid = threadIdx.x, lane = tid & 31u;
+  const uint32_t p0 = blockIdx.x * POS_TILE;
+  const uint32_t p = p0 + tid * POS_PER;
+  const bool use_mask = (a.work & HPGQ_WORK_FILTER) != 0 && a.mask != nullptr;
+  pos_queue qu;
+  qu.next = blockIdx.y * reads_per_slab;
+  qu.end = min(a.n_reads, qu.next + reads_per_slab);
+  qu.pend = 0u;
+  qu.my_o = qu.my_L = 0u;
+#pragma unroll
+  for (int t = 0; t < 6 * POS_PER; ++t) sacc[t * POS_THREADS + tid] = 0u;
+  uint32_t pk[5][2] = {{0u, 0u}, {0u, 0u}, {0u, 0u}, {0u, 0u}, {0u, 0u}};  // 8-bit lanes: A C G T N
+  uint32_t q16[2][2] = {{0u, 0u}, {0u, 0u}};                               // 16-bit lanes: (byte0, byte2), (byte1, byte3)
+  uint32_t since = 0;
+  bool more = true;
+
+  while (more) {
+    uint32_t oo[POS_BATCH], LL[POS_BATCH];
+#pragma unroll
+    for (int k = 0; k < POS_BATCH; ++k) {
+      oo[k] = 0u;
+      LL[k] = 0u;
+      if (more) more = pos_pop(a, qu, p0, use_mask, lane, oo[k], LL[k]);
+      if (!more) LL[k] = 0u;
+    }
+    uint32_t sv[POS_BATCH][2], qv[POS_BATCH][2];
+#pragma unroll
+    for (int k = 0; k < POS_BATCH; ++k) {
+      sv[k][0] = sv[k][1] = qv[k][0] = qv[k][1] = 0u;
+      if (p < LL[k]) {
+        load8(a.seq, oo[k] + p, sv[k][0], sv[k][1]);
+        load8(a.qual, oo[k] + p, qv[k][0], qv[k][1]);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < POS_BATCH; ++k) {
+#pragma unroll
+      for (int w = 0; w < 2; ++w) {
+        const uint32_t m = hq_tail_mask(p + 4u * w, LL[k]);
+        const uint32_t m1 = m & 0x01010101u, s = sv[k][w], qm = qv[k][w] & m;
+        pk[0][w] += __vcmpeq4(s, 0x41414141u) & m1;
+        pk[1][w] += __vcmpeq4(s, 0x43434343u) & m1;
+        pk[2][w] += __vcmpeq4(s, 0x47474747u) & m1;
+        pk[3][w] += __vcmpeq4(s, 0x54545454u) & m1;
+        pk[4][w] += __vcmpeq4(s, 0x4E4E4E4Eu) & m1;
+        q16[0][w] += __byte_perm(qm, 0u, 0x4240u);
+        q16[1][w] += __byte_perm(qm, 0u, 0x4341u);
+      }
+    }
+    since += POS_BATCH;
+    if (since > 255u - POS_BATCH || !more) {  // widen before an 8-bit (or 16-bit) lane can overflow
+#pragma unroll
+      for (int w = 0; w < 2; ++w) {
+#pragma unroll
+        for (int t = 0; t < 5; ++t) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            sacc[((1 + t) * POS_PER + 4 * w + i) * POS_THREADS + tid] += (pk[t][w] >> (8 * i)) & 0xFFu;
+          pk[t][w] = 0u;
+        }
+        sacc[(4 * w + 0) * POS_THREADS + tid] += q16[0][w] & 0xFFFFu;
+        sacc[(4 * w + 2) * POS_THREADS + tid] += q16[0][w] >> 16;
+        sacc[(4 * w + 1) * POS_THREADS + tid] += q16[1][w] & 0xFFFFu;
+        sacc[(4 * w + 3) * POS_THREADS + tid] += q16[1][w] >> 16;
+        q16[0][w] = q16[1][w] = 0u;
+      }
+      since = 0;
+    }
+  }
+  unsigned long long *C = a.ctr;
+  const uint32_t sec[6] = {a.o_accq, a.o_A, a.o_C, a.o_G, a.o_T, a.o_N};
+#pragma unroll
+  for (int t = 0; t < 6; ++t)
+#pragma unroll
+    for (int i = 0; i < POS_PER; ++i) {
+      const uint32_t v = sacc[(t * POS_PER + i) * POS_THREADS + tid];
+      if (v && p + i < a.Lcap) atomicAdd(&C[sec[t] + p + i], (unsigned long long)v);
+    }
+}
+
+}  // namespace
+
+cudaError_t hq_launch_qc_group(const hq_kargs &a, uint32_t max_len_in_batch, int sm_count, cudaStream_t st,
+                               uint64_t *launches) {
+  if (a.n_reads == 0) return cudaSuccess;
+  // lanes per read: one 16-byte chunk per lane covers the longest read (at any byte phase) when it is short
+  // enough -> register-resident kernel; longer reads loop over chunks with a whole warp per read
+  const uint32_t span = max_len_in_batch + 15u;  // bytes from the 16-byte boundary below the read start to its end
+  const int G = span <= 4u * RG_LB ? 4 : span <= 8u * RG_LB ? 8 : span <= 16u * RG_LB ? 16 : 32;
+  const bool regs = span <= 32u * RG_LB;
+  const uint32_t reads_per_block = (256u / (uint32_t)G) * (regs ? 2u : 1u);
+  uint32_t blocks = (a.n_reads + reads_per_block - 1u) / reads_per_block;
+  const uint32_t cap = (uint32_t)sm_count * 8u * 4u;
+  if (blocks > cap) blocks = cap;
+  if (regs) {
+    switch (G) {
+      case 4: hq_qc_regs_kernel<4><<<blocks, 256, 0, st>>>(a); break;
+      case 8: hq_qc_regs_kernel<8><<<blocks, 256, 0, st>>>(a); break;
+      case 16: hq_qc_regs_kernel<16><<<blocks, 256, 0, st>>>(a); break;
+      default: hq_qc_regs_kernel<32><<<blocks, 256, 0, st>>>(a); break;
+    }
+  } else {
+    hq_qc_group_kernel<32><<<blocks, 256, 0, st>>>(a);
+  }
+  ++*launches;
+  return cudaGetLastError();
+}
+
+cudaError_t hq_launch_pos(const hq_kargs &a, uint32_t max_len_in_batch, int sm_count, cudaStream_t st,
+                          uint64_t *launches) {
+  if (a.n_reads == 0 || max_len_in_batch == 0) return cudaSuccess;
+  const uint32_t cover = max_len_in_batch < a.Lcap ? max_len_in_batch : a.Lcap;
+  const uint32_t tiles = (cover + POS_TILE - 1u) / POS_TILE;
+  // 2 CTAs are resident per SM (48 KB of shared memory, <= 128 registers): two full waves
+  uint32_t slabs = ((uint32_t)sm_count * 4u) / tiles;
+  // a thread widens its packed lanes every 248 reads and keeps u32 sums: any slab size is safe below 2^24 reads
+  if (slabs > a.n_reads) slabs = a.n_reads;
+  if (slabs < 1u) slabs = 1u;
+  if (slabs > 65535u) slabs = 65535u;
+  const uint32_t reads_per_slab = (a.n_reads + slabs - 1u) / slabs;
+  hq_pos_kernel<<<dim3(tiles, slabs), POS_THREADS, 0, st>>>(a, reads_per_slab);
+  ++*launches;
+  return cudaGetLastError();
+}

@@ -49,6 +49,11 @@ cudaError_t hq_launch_qc_simple(const hq_kargs &a, cudaStream_t st, uint64_t *la
 cudaError_t hq_launch_qc_tiled(hq_kargs a, uint32_t max_len_in_batch, int sm_count, cudaStream_t st,
                                uint64_t *launches);
 bool hq_tiled_supports(uint32_t max_len_in_batch, uint32_t work);
+// vectorised any-length path (hpgq_group.cu): decisions + per-read histograms, then per-position tables
+cudaError_t hq_launch_qc_group(const hq_kargs &a, uint32_t max_len_in_batch, int sm_count, cudaStream_t st,
+                               uint64_t *launches);
+cudaError_t hq_launch_pos(const hq_kargs &a, uint32_t max_len_in_batch, int sm_count, cudaStream_t st,
+                          uint64_t *launches);
 cudaError_t hq_launch_kmers_cg(const hq_kargs &a, cudaStream_t st, uint64_t *launches);
 cudaError_t hq_launch_maxlen(const uint32_t *idx, uint32_t n, uint32_t *d_out, cudaStream_t st, uint64_t *launches);
 
@@ -59,7 +64,8 @@ struct hq_compact_bufs {
   uint32_t *out_idx, *out_src; // n+1 / n
   uint32_t *totals;            // [0]=n_passed [1]=n_failed [2]=passed_bytes [3]=failed_bytes (device)
 };
-cudaError_t hq_launch_compact(const hq_kargs &a, const hq_compact_bufs &b, cudaStream_t st, uint64_t *launches);
+cudaError_t hq_launch_compact(const hq_kargs &a, const hq_compact_bufs &b, uint32_t mean_len, cudaStream_t st,
+                              uint64_t *launches);
 
 cudaError_t hq_launch_synth(const hpgq_synth_cfg_t &cfg, uint64_t first_read, uint32_t n, uint8_t *d_seq,
                             uint8_t *d_qual, const uint32_t *d_idx, cudaStream_t st, uint64_t *launches);

@@ -235,3 +235,50 @@ def test_checksum_of_checksums_full_shape(q, ob):
     assert sum(int(c[S[k]]) for k in ("NUM_A", "NUM_C", "NUM_G", "NUM_T", "NUM_N")) == int(c[S["ACC_LENGTH"]])
     assert int(lay.section(c, "SUMQ_BY_LEN").sum()) == int(lay.section(c, "POS_ACCQ").sum())
     assert int(lay.section(c, "QUAL_HIST").sum()) == int(c[S["NUM_READS"]]) == int(lay.section(c, "GC_HIST").sum())
+
+
+def test_long_reads_group_and_position_kernels(q, ob):
+    """Config C5 shape (variable 1-20 kb reads): the vectorised group kernel (decisions, per-read histograms) and the
+    column-owner position kernel (per-position tables) against the oracle, with window filters, foreign bytes and a
+    quality byte >= 128; plus a mixed batch where a few long reads sit among short ones."""
+    cfg = q.synth_cfg((1000, 20000), seed=5)
+    seq, qual, idx = q.synth_host(cfg, 0, 1500)
+    seq, qual = seq.copy(), qual.copy()
+    seq[1000:1010] = np.frombuffer(b"acgtnRYKM.", dtype=np.uint8)
+    qual[50000] = 200
+    for flt in (dict(min_read_length=2000, min_read_quality=30, max_N=80),
+                dict(min_read_quality=20, max_read_quality=38, max_out_of_quality=4000, left_length=300,
+                     min_left_quality=30, right_length=500, min_right_quality=22, max_right_quality=40)):
+        par = q.make_params(q.WORK_STATS | q.WORK_FILTER, filter=flt)
+        _, res, _, emask, _ = check(q, ob, par, seq, qual, idx, 20032)
+        assert 0 < int(emask.sum()) < len(emask)
+    check(q, ob, q.make_params(q.WORK_STATS), seq, qual, idx, 20032)
+    # a batch holding a read longer than hpgq_limits_t.max_read_len is refused loudly when statistics are on
+    with pytest.raises(q.HpgqError, match="max_read_len"):
+        run_gpu(q, q.make_params(q.WORK_STATS), seq, qual, idx, 9984)
+    rng = np.random.default_rng(3)
+    s1, q1, i1 = rand_batch(rng, 4000, 0, 300, p_n=0.02)
+    s2, q2, i2 = rand_batch(rng, 30, 5000, 9000, p_n=0.01)
+    seq = np.concatenate([s1, s2])
+    qual = np.concatenate([q1, q2])
+    idx = np.concatenate([i1, i2[1:] + i1[-1]]).astype(np.uint32)
+    check(q, ob, q.make_params(q.WORK_STATS | q.WORK_FILTER, filter=dict(min_read_length=100, max_N=3)), seq, qual, idx, 9024)
+
+
+@pytest.mark.parametrize("lmax", [20, 60, 110, 300, 700, 2500])
+def test_edit_group_kernel_all_lane_widths(q, ob, lmax):
+    """EDIT + FILTER (+ filter windows) on ragged reads: every lanes-per-read instantiation of the group kernel."""
+    rng = np.random.default_rng(lmax)
+    seq, qual, idx = rand_batch(rng, 6000, 0, lmax, p_n=0.03)
+    qual = rng.integers(35, 74, size=len(qual)).astype(np.uint8)
+    par = q.make_params(q.WORK_EDIT | q.WORK_FILTER | q.WORK_COMPACT,
+                        edit=dict(left_length=7, min_left_quality=22, max_left_quality=25, right_length=9,
+                                  min_right_quality=19, max_right_quality=24),
+                        filter=dict(min_read_length=5, min_read_quality=20, max_read_quality=22, max_N=4,
+                                    max_out_of_quality=lmax // 2 + 3, left_length=4, min_left_quality=15,
+                                    max_left_quality=26, right_length=5, min_right_quality=14, max_right_quality=27))
+    _, res, _, emask, etrim = check(q, ob, par, seq, qual, idx, lmax + 8)
+    assert 0 < int(emask.sum()) < len(emask)
+    cp = ob.compact(seq, qual, idx, emask, etrim)
+    for k in ("out_idx", "out_src", "out_seq", "out_qual"):
+        assert np.array_equal(res[k], cp[k]), k
