@@ -160,37 +160,45 @@ __global__ void __launch_bounds__(256) hq_compact_copy(hq_kargs a, hq_compact_bu
     for (uint32_t k0 = 0; k0 < nch; k0 += G) {
       const uint32_t k = k0 + lig;
       const uint32_t dc = db + 16u * k;
-      const bool head = k < nch && dc < dst;                     // first chunk, starts before the read
-      const bool full = k < nch && !head && de - dc >= 16u;
-      // valid destination bytes of the chunk and the source byte that lands on the first of them
-      const uint32_t lo = head ? dst : dc, hi = (k < nch && de - dc >= 16u) ? dc + 16u : de;
-      const uint32_t sa = so + (lo - dst);
-      const bool ld = k <= nch;  // chunk nch only feeds the B half of chunk nch-1
+      // valid bytes [vlo, vhi) of this destination chunk
+      const uint32_t vlo = (k < nch && dc < dst) ? dst - dc : 0u;
+      const uint32_t vhi = k >= nch ? 0u : (de - dc >= 16u ? 16u : de - dc);
+      // source byte that lands on byte 0 of the chunk; for the head chunk it may lie before the read (and, for
+      // the first read of the batch, before the array: then the A half is not loaded, none of its bytes is used)
+      const uint32_t sa = so + (dc - dst);
+      const bool under = dc < dst && so < dst - dc;
       uint4 As = make_uint4(0, 0, 0, 0), Aq = As;
-      if (ld) {
+      if (k <= nch && !under) {  // chunk nch only feeds the B half of chunk nch-1
         As = __ldg(reinterpret_cast<const uint4 *>(a.seq + (sa & ~15u)));
         Aq = __ldg(reinterpret_cast<const uint4 *>(a.qual + (sa & ~15u)));
       }
       uint4 Bs = shfl_down4(As, gmask), Bq = shfl_down4(Aq, gmask);
-      // the head chunk has its own source phase, and the last lane's neighbour belongs to the next round
-      if ((head || lig == G - 1) && k < nch && (sa & 15u)) {
+      if (lig == G - 1 && k < nch && sh) {  // the neighbour belongs to the next round
         Bs = __ldg(reinterpret_cast<const uint4 *>(a.seq + (sa & ~15u) + 16u));
         Bq = __ldg(reinterpret_cast<const uint4 *>(a.qual + (sa & ~15u) + 16u));
       }
-      if (k < nch) {
-        const uint4 vs = shift_pair(As, Bs, sa & 15u), vq = shift_pair(Aq, Bq, sa & 15u);
-        if (full) {
+      if (vhi > vlo) {
+        const uint4 vs = shift_pair(As, Bs, sh), vq = shift_pair(Aq, Bq, sh);
+        if (vhi - vlo == 16u) {
           *reinterpret_cast<uint4 *>(b.out_seq + dc) = vs;
           *reinterpret_cast<uint4 *>(b.out_qual + dc) = vq;
-        } else {  // partial chunk: the bytes are in registers, predicated byte stores
-          const uint32_t cnt = hi - lo;
+        } else {  // partial chunk at an end of the read: whole words where possible, bytes for the rest
           const uint32_t ws[4] = {vs.x, vs.y, vs.z, vs.w}, wq[4] = {vq.x, vq.y, vq.z, vq.w};
 #pragma unroll
-          for (int t = 0; t < 15; ++t)
-            if ((uint32_t)t < cnt) {
-              b.out_seq[lo + t] = (uint8_t)(ws[t >> 2] >> (8 * (t & 3)));
-              b.out_qual[lo + t] = (uint8_t)(wq[t >> 2] >> (8 * (t & 3)));
+          for (int w = 0; w < 4; ++w) {
+            const uint32_t w0 = 4u * w;
+            if (vlo <= w0 && vhi >= w0 + 4u) {
+              *reinterpret_cast<uint32_t *>(b.out_seq + dc + w0) = ws[w];
+              *reinterpret_cast<uint32_t *>(b.out_qual + dc + w0) = wq[w];
+            } else if (vlo < w0 + 4u && vhi > w0) {
+#pragma unroll
+              for (int t = 0; t < 4; ++t)
+                if (w0 + t >= vlo && w0 + t < vhi) {
+                  b.out_seq[dc + w0 + t] = (uint8_t)(ws[w] >> (8 * t));
+                  b.out_qual[dc + w0 + t] = (uint8_t)(wq[w] >> (8 * t));
+                }
             }
+          }
         }
       }
     }

@@ -11,6 +11,7 @@
 //                           sums are register accumulators -- no atomics in the loop; the grid is
 //                           (position tiles) x (read slabs).
 // Both read HBM with full 128-byte-and-wider warp requests; the second kernel re-reads the batch (2 passes).
+#include <stdlib.h>
 #include "hpgq_dev.cuh"
 #include "hpgq_internal.h"
 
@@ -399,115 +400,198 @@ __device__ __forceinline__ void load8(const uint8_t *base, uint32_t off, uint32_
   v1 = (uint32_t)(v >> 32);
 }
 
-// Per-warp queue of the slab's reads that cover this position tile: 32 idx entries are tested per coalesced
-// load, the hits are handed out one by one with shuffles (every warp of the CTA walks the same list).
-struct pos_queue {
-  uint32_t next, end, pend, my_o, my_L;
+// Shared-memory ring filled with 16-byte cp.async copies issued by ALL threads of the CTA: warp 0 looks up the next
+// POS_RB reads that cover the tile and publishes their (offset, bytes, length) in the stage's header one iteration
+// ahead; after the iteration's barrier every thread copies its share of the 16-byte aligned supersets of the tile's
+// bytes and lets the copies arrive on the stage's mbarrier (cp.async.mbarrier.arrive.noinc); every warp then takes
+// its eight positions of each read from shared memory.  NS - 1 stages (of POS_RB reads x 2 x 2 KB) are in flight per
+// CTA, so HBM latency is hidden without spending registers on loads.  (One 1-D bulk copy per read and array was
+// measured first: ~0.7 M copies of 2 KB per launch sustain only 1.9 TB/s, the TMA engine is op-rate bound there.)
+constexpr int POS_RB = 4;                      // reads per stage
+constexpr int POS_NS = 4;                      // ring depth
+constexpr int POS_SLOT = POS_TILE + 32;        // bytes per read and array in a stage (16-byte aligned superset)
+constexpr int POS_CH = POS_SLOT / 16;          // 16-byte chunks per slot
+
+struct pos_entry {
+  uint32_t ga;     // batch offset of the 16-byte aligned superset of the tile's bytes of one read
+  uint32_t gb;     // its size in bytes (multiple of 16)
+  uint32_t L;      // read length
+  uint32_t delta;  // offset of position p0 inside the superset
+};
+constexpr int POS_FIFO = 128;  // descriptors; live range at any time < 4 * (NS + 2) + 32
+
+struct pos_smem {
+  uint64_t full[POS_NS];
+  uint32_t total;  // number of descriptors of the slab once the scan is over, 0xFFFFFFFF before
+  uint32_t pad[7];
+  pos_entry fifo[POS_FIFO];
+  alignas(16) uint8_t buf[POS_NS][POS_RB][2][POS_SLOT];
 };
 
-__device__ __forceinline__ bool pos_pop(const hq_kargs &a, pos_queue &qu, uint32_t p0, bool use_mask, uint32_t lane,
-                                        uint32_t &o, uint32_t &L) {
-  while (qu.pend == 0u) {
-    if (qu.next >= qu.end) return false;
-    const uint32_t r = qu.next + lane;
-    bool ok = false;
-    if (r < qu.end) {
-      qu.my_o = a.idx[r];
-      qu.my_L = a.idx[r + 1] - qu.my_o;
-      ok = qu.my_L > p0 && qu.my_L <= a.Lcap && (!use_mask || a.mask[r]);
-    }
-    qu.pend = __ballot_sync(0xFFFFFFFFu, ok);
-    qu.next += 32u;
-  }
-  const int src = __ffs(qu.pend) - 1;
-  qu.pend &= qu.pend - 1u;
-  o = __shfl_sync(0xFFFFFFFFu, qu.my_o, src);
-  L = __shfl_sync(0xFFFFFFFFu, qu.my_L, src);
-  return true;
+__device__ __forceinline__ void hq_cp_async16(void *dst_smem, const void *src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(hq_smem_u32(dst_smem)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void hq_cp_async_arrive_noinc(uint64_t *bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(hq_smem_u32(bar)) : "memory");
+}
+
+// eight bytes at any byte offset of a shared-memory slot
+__device__ __forceinline__ void lds8(const uint8_t *slot, uint32_t x, uint32_t &v0, uint32_t &v1) {
+  const unsigned long long *w = reinterpret_cast<const unsigned long long *>(slot + (x & ~7u));
+  const unsigned long long lo = w[0], hi = w[1];
+  const uint32_t sh = (x & 7u) * 8u;
+  const unsigned long long v = sh ? ((lo >> sh) | (hi << (64u - sh))) : lo;
+  v0 = (uint32_t)v;
+  v1 = (uint32_t)(v >> 32);
 }
 
 __global__ void __launch_bounds__(POS_THREADS, 2) hq_pos_kernel(hq_kargs a, uint32_t reads_per_slab) {
-  // widened sums of the owned positions, [table][position-in-thread][thread]: thread-private cells (no atomics),
-  // kept in shared memory only to leave the registers to the loads in flight
-  __shared__ uint32_t sacc[6 * POS_PER * POS_THREADS];
-  const uint32_t tid = threadIdx.x, lane = tid & 31u;
+  extern __shared__ __align__(128) uint8_t pos_raw[];
+  pos_smem &sm = *reinterpret_cast<pos_smem *>(pos_raw);
+  const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
   const uint32_t p0 = blockIdx.x * POS_TILE;
   const uint32_t p = p0 + tid * POS_PER;
   const bool use_mask = (a.work & HPGQ_WORK_FILTER) != 0 && a.mask != nullptr;
-  pos_queue qu;
-  qu.next = blockIdx.y * reads_per_slab;
-  qu.end = min(a.n_reads, qu.next + reads_per_slab);
-  qu.pend = 0u;
-  qu.my_o = qu.my_L = 0u;
+  if (tid == 0) {
+    for (int s = 0; s < POS_NS; ++s) hq_mbar_init(&sm.full[s], POS_THREADS);
+    hq_mbar_init_fence();
+  }
+
+  if (tid == 0) sm.total = 0xFFFFFFFFu;
+  // ---- warp 0: scan of the slab's reads, 32 per step; the lanes whose read covers the tile append its descriptor
+  // to the FIFO at (appended + rank among the hits).  The idx / mask loads of the next step are already in flight.
+  uint32_t scan = blockIdx.y * reads_per_slab;
+  const uint32_t scan_end = min(a.n_reads, scan + reads_per_slab);
+  uint32_t appended = 0, po = 0, pe = 0, pm = 0;
+  bool exhausted = scan >= scan_end;
+  auto prefetch = [&]() {
+    const uint32_t r = scan + lane;
+    const bool valid = r < scan_end;
+    po = valid ? a.idx[r] : 0u;
+    pe = valid ? a.idx[r + 1] : 0u;
+    pm = valid ? (use_mask ? (uint32_t)a.mask[r] : 1u) : 0u;
+  };
+  if (warp == 0 && !exhausted) prefetch();
+  auto produce = [&](uint32_t need) {
+    while (appended < need && !exhausted) {
+      const uint32_t o = po, L = pe - po;
+      const bool ok = pm != 0u && L > p0 && L <= a.Lcap;
+      scan += 32u;
+      if (scan < scan_end) prefetch();
+      else exhausted = true;
+      const uint32_t bal = __ballot_sync(0xFFFFFFFFu, ok);
+      if (ok) {
+        const uint32_t first = o + p0, ga = first & ~15u;
+        const uint32_t last = o + min(L, p0 + (uint32_t)POS_TILE);
+        pos_entry e;
+        e.ga = ga;
+        e.gb = ((last - ga) + 15u) & ~15u;
+        e.L = L;
+        e.delta = first - ga;
+        sm.fifo[(appended + __popc(bal & ((1u << lane) - 1u))) % POS_FIFO] = e;
+      }
+      appended += __popc(bal);
+    }
+    if (exhausted && lane == 0) sm.total = appended;
+  };
+  // all threads: copies of the stage of iteration j, arriving on its barrier
+  auto issue = [&](uint32_t j) {
+    const uint32_t s = j % POS_NS, tot = sm.total;
+    for (uint32_t i = tid; i < (uint32_t)(2 * POS_RB * POS_CH); i += POS_THREADS) {
+      const uint32_t pair = i / POS_CH, ch = i - pair * POS_CH, k = pair >> 1, arr = pair & 1u;
+      const uint32_t ei = POS_RB * j + k;
+      if (ei < tot) {
+        const pos_entry e = sm.fifo[ei % POS_FIFO];
+        if (16u * ch < e.gb) hq_cp_async16(sm.buf[s][k][arr] + 16u * ch, (arr ? a.qual : a.seq) + e.ga + 16u * ch);
+      }
+    }
+    hq_cp_async_arrive_noinc(&sm.full[s]);
+  };
+
+  uint32_t acc[6][POS_PER];  // quality sum, A, C, G, T, N per owned position
 #pragma unroll
-  for (int t = 0; t < 6 * POS_PER; ++t) sacc[t * POS_THREADS + tid] = 0u;
+  for (int t = 0; t < 6; ++t)
+#pragma unroll
+    for (int i = 0; i < POS_PER; ++i) acc[t][i] = 0u;
   uint32_t pk[5][2] = {{0u, 0u}, {0u, 0u}, {0u, 0u}, {0u, 0u}, {0u, 0u}};  // 8-bit lanes: A C G T N
   uint32_t q16[2][2] = {{0u, 0u}, {0u, 0u}};                               // 16-bit lanes: (byte0, byte2), (byte1, byte3)
   uint32_t since = 0;
-  bool more = true;
 
-  while (more) {
-    uint32_t oo[POS_BATCH], LL[POS_BATCH];
+  if (warp == 0) produce(POS_RB * POS_NS);
+  __syncthreads();  // barriers initialised, first descriptors visible
+  for (uint32_t j = 0; j + 1 < POS_NS; ++j) issue(j);
+
+  for (uint32_t it = 0;; ++it) {
+    const uint32_t s = it % POS_NS;
+    // descriptors of iteration it + NS (one iteration ahead of their copies), then the barrier that (a) publishes the
+    // descriptors written in the previous iteration and (b) guarantees everybody is done with the stage to be refilled
+    if (warp == 0) produce(POS_RB * (it + POS_NS + 1u));
+    __syncthreads();
+    issue(it + POS_NS - 1u);
+    hq_mbar_wait(&sm.full[s], (it / POS_NS) & 1u);
+    const uint32_t tot = sm.total;
+    if (tot <= POS_RB * it) break;
 #pragma unroll
-    for (int k = 0; k < POS_BATCH; ++k) {
-      oo[k] = 0u;
-      LL[k] = 0u;
-      if (more) more = pos_pop(a, qu, p0, use_mask, lane, oo[k], LL[k]);
-      if (!more) LL[k] = 0u;
-    }
-    uint32_t sv[POS_BATCH][2], qv[POS_BATCH][2];
+    for (int k = 0; k < POS_RB; ++k) {
+      const uint32_t ei = POS_RB * it + k;
+      const pos_entry e = sm.fifo[ei % POS_FIFO];
+      const uint32_t L = ei < tot ? e.L : 0u;
+      if (p < L && !(a.work & 0x8000u)) {
+        const uint32_t x = e.delta + tid * POS_PER;
+        uint32_t sv[2], qv[2];
+        lds8(sm.buf[s][k][0], x, sv[0], sv[1]);
+        lds8(sm.buf[s][k][1], x, qv[0], qv[1]);
 #pragma unroll
-    for (int k = 0; k < POS_BATCH; ++k) {
-      sv[k][0] = sv[k][1] = qv[k][0] = qv[k][1] = 0u;
-      if (p < LL[k]) {
-        load8(a.seq, oo[k] + p, sv[k][0], sv[k][1]);
-        load8(a.qual, oo[k] + p, qv[k][0], qv[k][1]);
+        for (int w = 0; w < 2; ++w) {
+          const uint32_t m = hq_tail_mask(p + 4u * w, L);
+          const uint32_t sw = sv[w] & m, qm = qv[w] & m;  // bytes past the read end become 0x00: no symbol
+          pk[0][w] += rg_zero_flags(sw ^ 0x41414141u) >> 7;
+          pk[1][w] += rg_zero_flags(sw ^ 0x43434343u) >> 7;
+          pk[2][w] += rg_zero_flags(sw ^ 0x47474747u) >> 7;
+          pk[3][w] += rg_zero_flags(sw ^ 0x54545454u) >> 7;
+          pk[4][w] += rg_zero_flags(sw ^ 0x4E4E4E4Eu) >> 7;
+          q16[0][w] += __byte_perm(qm, 0u, 0x4240u);
+          q16[1][w] += __byte_perm(qm, 0u, 0x4341u);
+        }
       }
     }
-#pragma unroll
-    for (int k = 0; k < POS_BATCH; ++k) {
-#pragma unroll
-      for (int w = 0; w < 2; ++w) {
-        const uint32_t m = hq_tail_mask(p + 4u * w, LL[k]);
-        const uint32_t m1 = m & 0x01010101u, s = sv[k][w], qm = qv[k][w] & m;
-        pk[0][w] += __vcmpeq4(s, 0x41414141u) & m1;
-        pk[1][w] += __vcmpeq4(s, 0x43434343u) & m1;
-        pk[2][w] += __vcmpeq4(s, 0x47474747u) & m1;
-        pk[3][w] += __vcmpeq4(s, 0x54545454u) & m1;
-        pk[4][w] += __vcmpeq4(s, 0x4E4E4E4Eu) & m1;
-        q16[0][w] += __byte_perm(qm, 0u, 0x4240u);
-        q16[1][w] += __byte_perm(qm, 0u, 0x4341u);
-      }
-    }
-    since += POS_BATCH;
-    if (since > 255u - POS_BATCH || !more) {  // widen before an 8-bit (or 16-bit) lane can overflow
+    since += POS_RB;
+    if (since > 255u - POS_RB) {  // widen before an 8-bit (or 16-bit) lane can overflow
 #pragma unroll
       for (int w = 0; w < 2; ++w) {
 #pragma unroll
         for (int t = 0; t < 5; ++t) {
 #pragma unroll
-          for (int i = 0; i < 4; ++i)
-            sacc[((1 + t) * POS_PER + 4 * w + i) * POS_THREADS + tid] += (pk[t][w] >> (8 * i)) & 0xFFu;
+          for (int i = 0; i < 4; ++i) acc[1 + t][4 * w + i] += (pk[t][w] >> (8 * i)) & 0xFFu;
           pk[t][w] = 0u;
         }
-        sacc[(4 * w + 0) * POS_THREADS + tid] += q16[0][w] & 0xFFFFu;
-        sacc[(4 * w + 2) * POS_THREADS + tid] += q16[0][w] >> 16;
-        sacc[(4 * w + 1) * POS_THREADS + tid] += q16[1][w] & 0xFFFFu;
-        sacc[(4 * w + 3) * POS_THREADS + tid] += q16[1][w] >> 16;
+        acc[0][4 * w + 0] += q16[0][w] & 0xFFFFu;
+        acc[0][4 * w + 2] += q16[0][w] >> 16;
+        acc[0][4 * w + 1] += q16[1][w] & 0xFFFFu;
+        acc[0][4 * w + 3] += q16[1][w] >> 16;
         q16[0][w] = q16[1][w] = 0u;
       }
       since = 0;
     }
+  }
+#pragma unroll
+  for (int w = 0; w < 2; ++w) {
+#pragma unroll
+    for (int t = 0; t < 5; ++t)
+#pragma unroll
+      for (int i = 0; i < 4; ++i) acc[1 + t][4 * w + i] += (pk[t][w] >> (8 * i)) & 0xFFu;
+    acc[0][4 * w + 0] += q16[0][w] & 0xFFFFu;
+    acc[0][4 * w + 2] += q16[0][w] >> 16;
+    acc[0][4 * w + 1] += q16[1][w] & 0xFFFFu;
+    acc[0][4 * w + 3] += q16[1][w] >> 16;
   }
   unsigned long long *C = a.ctr;
   const uint32_t sec[6] = {a.o_accq, a.o_A, a.o_C, a.o_G, a.o_T, a.o_N};
 #pragma unroll
   for (int t = 0; t < 6; ++t)
 #pragma unroll
-    for (int i = 0; i < POS_PER; ++i) {
-      const uint32_t v = sacc[(t * POS_PER + i) * POS_THREADS + tid];
-      if (v && p + i < a.Lcap) atomicAdd(&C[sec[t] + p + i], (unsigned long long)v);
-    }
+    for (int i = 0; i < POS_PER; ++i)
+      if (acc[t][i] && p + i < a.Lcap) atomicAdd(&C[sec[t] + p + i], (unsigned long long)acc[t][i]);
 }
 
 }  // namespace
@@ -543,14 +627,20 @@ cudaError_t hq_launch_pos(const hq_kargs &a, uint32_t max_len_in_batch, int sm_c
   if (a.n_reads == 0 || max_len_in_batch == 0) return cudaSuccess;
   const uint32_t cover = max_len_in_batch < a.Lcap ? max_len_in_batch : a.Lcap;
   const uint32_t tiles = (cover + POS_TILE - 1u) / POS_TILE;
-  // 2 CTAs are resident per SM (48 KB of shared memory, <= 128 registers): two full waves
-  uint32_t slabs = ((uint32_t)sm_count * 4u) / tiles;
+  // 2 CTAs are resident per SM (67 KB ring each, <= 128 registers): four waves, the tiles near the longest reads
+  // see few reads and finish early
+  uint32_t slabs = ((uint32_t)sm_count * 8u) / tiles;
   // a thread widens its packed lanes every 248 reads and keeps u32 sums: any slab size is safe below 2^24 reads
   if (slabs > a.n_reads) slabs = a.n_reads;
   if (slabs < 1u) slabs = 1u;
   if (slabs > 65535u) slabs = 65535u;
   const uint32_t reads_per_slab = (a.n_reads + slabs - 1u) / slabs;
-  hq_pos_kernel<<<dim3(tiles, slabs), POS_THREADS, 0, st>>>(a, reads_per_slab);
+  hq_kargs a2 = a;
+  if (getenv("HPGQ_DEBUG_LOADONLY")) a2.work |= 0x8000u;  // developer probe: ring traffic without the arithmetic
+  // per device, so set on every launch (one process may drive several GPUs)
+  cudaError_t e = cudaFuncSetAttribute(hq_pos_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(pos_smem));
+  if (e != cudaSuccess) return e;
+  hq_pos_kernel<<<dim3(tiles, slabs), POS_THREADS, sizeof(pos_smem), st>>>(a2, reads_per_slab);
   ++*launches;
   return cudaGetLastError();
 }
