@@ -64,6 +64,7 @@ struct hpgq_ctx {
   bool have_params = false;
   hpgq_layout_t lay = {};
   unsigned long long *d_ctr = nullptr;
+  unsigned long long *d_cgpack = nullptr;  // packed chaos-game shadow table, always all-zero between batches
   hpgq_slot slot[HPGQ_MAX_SLOTS];
   uint64_t launches = 0;
   uint64_t batches = 0;
@@ -127,6 +128,16 @@ extern "C" int hpgq_counters_finalize_host(const hpgq_layout_t *lay, uint64_t *c
     for (uint32_t j = 0; j < Lcap; ++j) t += p[j];
     c[dst[k]] = t;
   }
+  // 5-mer totals = row sums of the 5-mer x start-position table (the device keeps only the table)
+  if (lay->kmers && lay->offset[HPGQ_SEC_K5 + 1] > lay->offset[HPGQ_SEC_K5]) {
+    uint64_t *k5 = c + lay->offset[HPGQ_SEC_K5];
+    const uint64_t *kp = c + lay->offset[HPGQ_SEC_K5_POS];
+    for (uint32_t id = 0; id < 1024; ++id) {
+      uint64_t t = 0;
+      for (uint32_t j = 0; j < Lcap; ++j) t += kp[(uint64_t)id * Lcap + j];
+      k5[id] = t;
+    }
+  }
   uint64_t mn = 100000, mx = 0;
   const uint64_t *h = c + lay->offset[HPGQ_SEC_LEN_HIST];
   for (uint32_t L = 0; L <= Lcap; ++L)
@@ -173,6 +184,7 @@ extern "C" int hpgq_ctx_destroy(hpgq_ctx_t *ctx) {
   cudaDeviceSynchronize();
   for (int i = 0; i < HPGQ_MAX_SLOTS; ++i) slot_free(ctx->slot[i]);
   cudaFree(ctx->d_ctr);
+  cudaFree(ctx->d_cgpack);
   delete ctx;
   return HPGQ_OK;
 }
@@ -205,6 +217,10 @@ extern "C" int hpgq_ctx_create(int device, const hpgq_limits_t *lim, hpgq_ctx_t 
   const size_t words = c->lay.offset[HPGQ_SEC_COUNT];
   cudaError_t e = cudaMalloc(&c->d_ctr, words * 8);
   if (e == cudaSuccess) e = cudaMemset(c->d_ctr, 0, words * 8);
+  if (e == cudaSuccess && lim->cg_k) {
+    e = cudaMalloc(&c->d_cgpack, (8ull << (2 * lim->cg_k)));
+    if (e == cudaSuccess) e = cudaMemset(c->d_cgpack, 0, (8ull << (2 * lim->cg_k)));
+  }
   const size_t nb = (size_t)lim->max_bytes_per_batch + 64, nr = (size_t)lim->max_reads_per_batch;
   for (uint32_t i = 0; i < c->lim.n_slots && e == cudaSuccess; ++i) {
     hpgq_slot &s = c->slot[i];

@@ -28,6 +28,7 @@ struct hq_kargs {
   unsigned long long *ctr;
   uint32_t o_len_hist, o_sumq, o_qual_hist, o_gc_hist, o_accq, o_A, o_C, o_G, o_T, o_N;
   uint64_t o_k5, o_k5pos, o_k2, o_cg_seq, o_cg_q;
+  unsigned long long *cg_pack; // packed chaos-game shadow table (count << 38 | quality sum), NULL = not used
   // per-read outputs
   uint8_t *mask;     // may be NULL
   hpgq_trim_t *trim; // may be NULL
@@ -54,7 +55,7 @@ cudaError_t hq_launch_qc_group(const hq_kargs &a, uint32_t max_len_in_batch, int
                                uint64_t *launches);
 cudaError_t hq_launch_pos(const hq_kargs &a, uint32_t max_len_in_batch, int sm_count, cudaStream_t st,
                           uint64_t *launches);
-cudaError_t hq_launch_kmers_cg(const hq_kargs &a, cudaStream_t st, uint64_t *launches);
+cudaError_t hq_launch_kmers_cg(const hq_kargs &a, uint32_t max_len_in_batch, cudaStream_t st, uint64_t *launches);
 cudaError_t hq_launch_maxlen(const uint32_t *idx, uint32_t n, uint32_t *d_out, cudaStream_t st, uint64_t *launches);
 
 struct hq_compact_bufs {

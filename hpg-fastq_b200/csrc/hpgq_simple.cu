@@ -130,12 +130,44 @@ __global__ void __launch_bounds__(256) hq_qc_simple_kernel(hq_kargs a) {
 // (SURVEY.md 8c(5)); chaos game = integer-index form of old/chaos_game.c:165-267.
 constexpr uint32_t HQ_LOOKBACK = 20;
 
+// One chaos-game word: table_seq[cell]++ and table_q[cell] += qval (old/chaos_game.c:253-259).  With a packed
+// shadow table both land in ONE 64-bit reduction, count in the top 26 bits and the quality sum in the low 38
+// (a sub-launch covers < 2^26 words and qval < 2^12, so neither field can overflow); hq_cg_unpack_kernel adds the
+// fields to the real tables afterwards.  Values outside [0, 4096) (qualities below the base quality wrap, as the
+// reference's unsigned arithmetic does) go to the real tables directly.
+__device__ __forceinline__ void cg_add(const hq_kargs &a, uint64_t cell, uint32_t qval) {
+  unsigned long long *C = a.ctr;
+  if (a.cg_pack && qval < 4096u) {
+    atomicAdd(&a.cg_pack[cell], (1ull << 38) | (unsigned long long)qval);
+  } else {
+    atomicAdd(&C[a.o_cg_seq + cell], 1ull);
+    atomicAdd(&C[a.o_cg_q + cell], (unsigned long long)qval);
+  }
+}
+
+__global__ void __launch_bounds__(256) hq_cg_unpack_kernel(hq_kargs a, uint32_t cells) {
+  unsigned long long *C = a.ctr;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < cells; i += gridDim.x * blockDim.x) {
+    const unsigned long long v = a.cg_pack[i];
+    if (v) {
+      C[a.o_cg_seq + i] += v >> 38;
+      C[a.o_cg_q + i] += v & ((1ull << 38) - 1ull);
+      a.cg_pack[i] = 0ull;
+    }
+  }
+}
+
 __device__ __forceinline__ int base2(uint32_t c) {
   return c == 'A' ? 0 : c == 'C' ? 1 : c == 'G' ? 2 : c == 'T' ? 3 : -1;
 }
 
+// G lanes share one read (G = 4 for short reads: the chunk of a lane is then much longer than the look-back that
+// warms its rolling state up; G = 32 for long reads).
+template <int G>
 __global__ void __launch_bounds__(256) hq_kmers_cg_kernel(hq_kargs a) {
-  const uint32_t lane = threadIdx.x & 31u;
+  constexpr uint32_t NG = 32u / G;
+  const uint32_t lane = threadIdx.x & 31u, lig = lane % G, giw = lane / G;
+  const uint32_t gmask = (G == 32 ? 0xFFFFFFFFu : ((1u << G) - 1u)) << (giw * G);
   const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
   const bool do_k = (a.work & HPGQ_WORK_KMERS) != 0, do_cg = (a.work & HPGQ_WORK_CHAOS) != 0 && a.cg_k > 0;
@@ -145,14 +177,15 @@ __global__ void __launch_bounds__(256) hq_kmers_cg_kernel(hq_kargs a) {
   unsigned long long *C = a.ctr;
   unsigned long long words = 0, longruns = 0;
 
-  for (uint32_t r = warp; r < a.n_reads; r += nwarps) {
-    const uint32_t o = a.idx[r], L = a.idx[r + 1] - o;
-    if (L == 0) continue;
+  for (uint32_t r0 = warp * NG; r0 < a.n_reads; r0 += nwarps * NG) {  // warp-uniform trip count (ballots below)
+    const uint32_t r = r0 + giw;
+    const bool live = r < a.n_reads;
+    const uint32_t o = live ? a.idx[r] : 0u, L = live ? a.idx[r + 1] - o : 0u;
     const uint8_t *s = a.seq + o, *q = a.qual + o;
-    const bool kmers_here = do_k && (!use_mask || a.mask[r]) && L <= a.Lcap;
+    const bool kmers_here = do_k && live && (!use_mask || a.mask[r]) && L <= a.Lcap;
     // does the read hold bytes other than A,C,G,T,N?  (changes the chaos-game window arithmetic)
     bool other = false, single_x = true, single_y = true;
-    for (uint32_t j = lane; j < L; j += 32) {
+    for (uint32_t j = lig; j < L; j += G) {
       const uint32_t c = s[j];
       const int b = base2(c);
       if (b < 0 && c != 'N') other = true;
@@ -161,13 +194,13 @@ __global__ void __launch_bounds__(256) hq_kmers_cg_kernel(hq_kargs a) {
         if (!(b == 2 || b == 3)) single_y = false;
       }
     }
-    other = __any_sync(0xFFFFFFFFu, other);
-    single_x = __all_sync(0xFFFFFFFFu, single_x);
-    single_y = __all_sync(0xFFFFFFFFu, single_y);
-    if (do_cg && lane == 0 && (single_x || single_y)) longruns++;
+    other = (__ballot_sync(0xFFFFFFFFu, other) & gmask) != 0u;
+    single_x = (__ballot_sync(0xFFFFFFFFu, single_x) & gmask) == gmask;
+    single_y = (__ballot_sync(0xFFFFFFFFu, single_y) & gmask) == gmask;
+    if (do_cg && lig == 0 && L != 0u && (single_x || single_y)) longruns++;
 
-    const uint32_t chunk = (L + 31u) / 32u;
-    const uint32_t cb = lane * chunk, ce = min(L, cb + chunk);
+    const uint32_t chunk = (L + (uint32_t)G - 1u) / (uint32_t)G;
+    const uint32_t cb = lig * chunk, ce = min(L, cb + chunk);
     if (cb < ce) {
       const uint32_t jb = cb > HQ_LOOKBACK ? cb - HQ_LOOKBACK : 0u;
       uint32_t code = 0, valid = 0; // k-mer rolling state
@@ -199,18 +232,13 @@ __global__ void __launch_bounds__(256) hq_kmers_cg_kernel(hq_kargs a) {
         if (j < cb) continue;
         if (b >= 0) {
           if (kmers_here) {
-            if (valid >= 5u) {
-              const uint32_t id = code & 1023u;
-              atomicAdd(&C[a.o_k5 + id], 1ull);
-              atomicAdd(&C[a.o_k5pos + (uint64_t)id * a.Lcap + (j - 4u)], 1ull);
-            }
+            // 5-mer x start position: hq_k5pos_kernel (shared-memory slices); the 5-mer totals are the row sums of
+            // that table, derived at download (hpgq_counters_finalize_host)
             if (k2 > 0 && valid >= (uint32_t)k2) atomicAdd(&C[a.o_k2 + (code & k2mask)], 1ull);
           }
           if (do_cg && !other) {
             if (cnt >= (uint32_t)ck) {
-              const uint64_t cell = ((uint64_t)ix << ck) + iy;
-              atomicAdd(&C[a.o_cg_seq + cell], 1ull);
-              atomicAdd(&C[a.o_cg_q + cell], (unsigned long long)(uint32_t)(accq - (uint32_t)(a.cg_base_quality * ck)));
+              cg_add(a, ((uint64_t)ix << ck) + iy, accq - (uint32_t)(a.cg_base_quality * ck));
               words++;
             }
             if (run_x == 21u || run_y == 21u) longruns++;
@@ -219,7 +247,7 @@ __global__ void __launch_bounds__(256) hq_kmers_cg_kernel(hq_kargs a) {
       }
     }
     // reads with other bytes: literal sequential emulation of the reference's positional window by lane 0
-    if (do_cg && other && lane == 0) {
+    if (do_cg && other && lig == 0) {
       uint32_t ix = 0, iy = 0, accq = 0, run_x = 0, run_y = 0;
       int cnt = 0;
       for (uint32_t j = 0; j < L; ++j) {
@@ -239,9 +267,7 @@ __global__ void __launch_bounds__(256) hq_kmers_cg_kernel(hq_kargs a) {
           accq = 0;
         }
         if (cnt == ck) {
-          const uint64_t cell = ((uint64_t)ix << ck) + iy;
-          atomicAdd(&C[a.o_cg_seq + cell], 1ull);
-          atomicAdd(&C[a.o_cg_q + cell], (unsigned long long)(uint32_t)(accq - (uint32_t)(a.cg_base_quality * ck)));
+          cg_add(a, ((uint64_t)ix << ck) + iy, accq - (uint32_t)(a.cg_base_quality * ck));
           words++;
           cnt--;
           accq -= (uint32_t)(int32_t)(signed char)q[j + 1 - ck];
@@ -262,6 +288,90 @@ __global__ void __launch_bounds__(256) hq_kmers_cg_kernel(hq_kargs a) {
   if (lane == 0) {
     if (words) atomicAdd(&C[HPGQ_S_CG_WORDS], words);
     if (longruns) atomicAdd(&C[HPGQ_S_CG_LONG_RUNS], longruns);
+  }
+}
+
+// ---------------------------------------------------------------- 5-mer x start-position table
+// kmer_t.counter_by_pos (reference src/stats_fastq.c:396-405).  One global atomic per base is what bounds the naive
+// kernel, so the table is privatised in shared memory by POSITION SLICE: a CTA owns K5_W start positions for a slab
+// of <= 65535 reads and keeps all 1024 x K5_W cells as 16-bit counters (a read adds at most 1 to a cell, so a slab
+// cannot overflow them); a warp stages the slice bytes of 32 reads with coalesced loads, then every lane rolls the
+// 2-bit code over its own read and bumps the cells with shared-memory atomics.  The table is flushed once per CTA.
+constexpr int K5_W = 48;                    // start positions per slice
+constexpr int K5_SW = (K5_W + 4 + 3 + 3) / 4 + 1;  // staged words per read: slice + 4 bases, any byte phase (23)
+constexpr int K5_STRIDE = K5_SW | 1;        // odd row stride: conflict-free lane-per-row access
+constexpr int K5_THREADS = 1024;
+constexpr int K5_ROW = K5_W / 2 + 1;        // words per 5-mer row, odd: rows of different 5-mers spread over all banks
+
+struct k5_smem {
+  uint32_t tab[1024 * K5_ROW];                          // u16 pairs
+  uint32_t stage[K5_THREADS / 32][32 * K5_STRIDE];
+};
+
+__global__ void __launch_bounds__(K5_THREADS, 1) hq_k5pos_kernel(hq_kargs a, uint32_t reads_per_slab) {
+  extern __shared__ __align__(16) uint8_t k5_raw[];
+  k5_smem &sm = *reinterpret_cast<k5_smem *>(k5_raw);
+  const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+  const uint32_t p0 = blockIdx.x * K5_W;
+  const bool use_mask = (a.work & HPGQ_WORK_FILTER) != 0 && a.mask != nullptr;
+  for (uint32_t i = tid; i < 1024u * K5_ROW; i += K5_THREADS) sm.tab[i] = 0u;
+  __syncthreads();
+  const uint32_t r_begin = blockIdx.y * reads_per_slab, r_end = min(a.n_reads, r_begin + reads_per_slab);
+  uint32_t *st = sm.stage[warp];
+  for (uint32_t g0 = r_begin + warp * 32u; g0 < r_end; g0 += (K5_THREADS / 32) * 32u) {
+    // my read of the group
+    const uint32_t r = g0 + lane;
+    uint32_t o = 0, L = 0;
+    if (r < r_end) {
+      o = a.idx[r];
+      L = a.idx[r + 1] - o;
+      if (L > a.Lcap || L < p0 + 5u || (use_mask && !a.mask[r])) L = 0;  // nothing to count in this slice
+    }
+    // stage: read i of the group <- lanes 0..K5_SW-1 load consecutive aligned words of its slice
+    const uint32_t any = __ballot_sync(0xFFFFFFFFu, L != 0u);
+    if (!any) continue;
+#pragma unroll 4
+    for (int i = 0; i < 32; ++i) {
+      const uint32_t oi = __shfl_sync(0xFFFFFFFFu, o, i), Li = __shfl_sync(0xFFFFFFFFu, L, i);
+      if (Li == 0u) continue;  // warp-uniform
+      const uint32_t first = oi + p0, wa = (first & ~3u) + 4u * lane;
+      const uint32_t last = oi + min(Li, p0 + (uint32_t)K5_W + 4u);  // one past the last byte needed
+      if (lane < (uint32_t)K5_SW && wa < last) st[i * K5_STRIDE + lane] = __ldg(reinterpret_cast<const uint32_t *>(a.seq + wa));
+    }
+    __syncwarp();
+    if (L) {
+      const uint32_t ph = (o + p0) & 3u;                       // byte phase of position p0 in the first staged word
+      const uint32_t nb = min(L - p0, (uint32_t)K5_W + 4u);    // bases of this read in the slice
+      const uint32_t *row = st + lane * K5_STRIDE;
+      uint32_t code = 0, valid = 0, w = 0;
+      for (uint32_t t = 0; t < nb; ++t) {
+        const uint32_t bi = ph + t;
+        if ((bi & 3u) == 0u || t == 0u) w = row[bi >> 2];
+        const uint32_t c = (w >> (8u * (bi & 3u))) & 0xFFu;
+        const uint32_t h = (c >> 1) & 3u, b2 = h ^ (h >> 1);   // A=0 C=1 G=2 T=3 for the four bases
+        if (((0x54474341u >> (8u * b2)) & 0xFFu) == c) {
+          code = ((code << 2) | b2) & 1023u;
+          valid++;
+          if (valid >= 5u) {
+            const uint32_t wp = t - 4u;                        // window starts at p0 + wp
+            atomicAdd(&sm.tab[code * K5_ROW + (wp >> 1)], (wp & 1u) ? 65536u : 1u);
+          }
+        } else {
+          valid = 0;
+        }
+      }
+    }
+    __syncwarp();
+  }
+  __syncthreads();
+  unsigned long long *C = a.ctr;
+  for (uint32_t i = tid; i < 1024u * K5_ROW; i += K5_THREADS) {
+    const uint32_t v = sm.tab[i];
+    if (v) {
+      const uint32_t id = i / K5_ROW, wpos = 2u * (i - id * K5_ROW);
+      if (v & 0xFFFFu) atomicAdd(&C[a.o_k5pos + (uint64_t)id * a.Lcap + p0 + wpos], (unsigned long long)(v & 0xFFFFu));
+      if (v >> 16) atomicAdd(&C[a.o_k5pos + (uint64_t)id * a.Lcap + p0 + wpos + 1u], (unsigned long long)(v >> 16));
+    }
   }
 }
 
@@ -296,12 +406,50 @@ cudaError_t hq_launch_qc_simple(const hq_kargs &a, cudaStream_t st, uint64_t *la
   return cudaGetLastError();
 }
 
-cudaError_t hq_launch_kmers_cg(const hq_kargs &a, cudaStream_t st, uint64_t *launches) {
-  if (a.n_reads == 0) return cudaSuccess;
-  uint32_t blocks = (a.n_reads + 7u) / 8u;
-  if (blocks > 148u * 16u) blocks = 148u * 16u;
-  hq_kmers_cg_kernel<<<blocks, 256, 0, st>>>(a);
-  ++*launches;
+cudaError_t hq_launch_kmers_cg(const hq_kargs &a0, uint32_t max_len_in_batch, cudaStream_t st, uint64_t *launches) {
+  if (a0.n_reads == 0) return cudaSuccess;
+  const bool cg = (a0.work & HPGQ_WORK_CHAOS) != 0 && a0.cg_k > 0;
+  // with the packed chaos-game table a sub-launch must stay below 2^26 words (see cg_add)
+  uint32_t chunk = a0.n_reads;
+  if (cg && a0.cg_pack) {
+    const uint64_t per = ((1ull << 26) - 1ull) / (max_len_in_batch ? max_len_in_batch : 1u);
+    if (per == 0) return cudaErrorInvalidValue;
+    if (per < chunk) chunk = (uint32_t)per;
+  }
+  if ((a0.work & HPGQ_WORK_KMERS) && max_len_in_batch >= 5u) {
+    const uint32_t cover = (max_len_in_batch < a0.Lcap ? max_len_in_batch : a0.Lcap) - 4u;  // window start positions
+    const uint32_t slices = (cover + K5_W - 1u) / K5_W;
+    const uint32_t min_slabs = (a0.n_reads + 65534u) / 65535u;  // 16-bit cells: at most 65535 reads per slab
+    // one CTA per SM is resident: make slices x slabs fill whole waves of 148 CTAs
+    uint32_t waves = (min_slabs * slices + 147u) / 148u, slabs = (148u * waves) / slices;
+    if (slabs < min_slabs) slabs = (148u * ++waves) / slices;
+    if (slabs < min_slabs) slabs = min_slabs;
+    if (slabs > a0.n_reads) slabs = a0.n_reads;
+    if (slabs > 65535u) slabs = 65535u;
+    const uint32_t reads_per_slab = (a0.n_reads + slabs - 1u) / slabs;
+    cudaError_t e = cudaFuncSetAttribute(hq_k5pos_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(k5_smem));
+    if (e != cudaSuccess) return e;
+    hq_k5pos_kernel<<<dim3(slices, slabs), K5_THREADS, sizeof(k5_smem), st>>>(a0, reads_per_slab);
+    ++*launches;
+  }
+  if (!(a0.work & HPGQ_WORK_CHAOS) && !((a0.work & HPGQ_WORK_KMERS) && a0.k2 > 0)) return cudaGetLastError();
+  for (uint32_t first = 0; first < a0.n_reads; first += chunk) {
+    hq_kargs a = a0;
+    a.n_reads = a0.n_reads - first < chunk ? a0.n_reads - first : chunk;
+    a.idx = a0.idx + first;
+    if (a.mask) a.mask = a0.mask + first;
+    const bool narrow = max_len_in_batch <= 1024u;
+    uint32_t blocks = (a.n_reads + (narrow ? 63u : 7u)) / (narrow ? 64u : 8u);
+    if (blocks > 148u * 16u) blocks = 148u * 16u;
+    if (narrow) hq_kmers_cg_kernel<4><<<blocks, 256, 0, st>>>(a);
+    else hq_kmers_cg_kernel<32><<<blocks, 256, 0, st>>>(a);
+    ++*launches;
+    if (cg && a.cg_pack) {
+      const uint32_t cells = 1u << (2 * a.cg_k);
+      hq_cg_unpack_kernel<<<(cells + 1023u) / 1024u < 592u ? (cells + 1023u) / 1024u : 592u, 256, 0, st>>>(a, cells);
+      ++*launches;
+    }
+  }
   return cudaGetLastError();
 }
 

@@ -145,7 +145,7 @@ enum hpgq_section {
   HPGQ_SEC_POS_G,
   HPGQ_SEC_POS_T,
   HPGQ_SEC_POS_N,
-  HPGQ_SEC_K5,     /* 1024 5-mer totals                  (kmer_t.counter)            */
+  HPGQ_SEC_K5,     /* 1024 5-mer totals (kmer_t.counter); row sums of K5_POS, derived at download */
   HPGQ_SEC_K5_POS, /* 1024 x Lcap, [id*Lcap + start_pos]  (kmer_t.counter_by_pos)     */
   HPGQ_SEC_K2,     /* 4^k2 totals                                                     */
   HPGQ_SEC_CG_SEQ, /* 2^cg_k x 2^cg_k, [co_x*dim + co_y]  (table_seq)                 */
