@@ -146,6 +146,19 @@ HQ_HDI hq_dec2_t hq_decode2(uint32_t swm) {
   return d;
 }
 
+// hq_decode2 with the low halves of the three LUTs held in registers by the caller (values pinned with an opaque
+// asm so that the compiler keeps them live instead of re-materialising a MOV per use)
+HQ_HDI hq_dec2_t hq_decode2_r(uint32_t swm, uint32_t lut_cg, uint32_t lut_at, uint32_t lut_e) {
+  hq_dec2_t d;
+  const uint32_t wp = hq_prmt(swm, 0u, 0x3120u);
+  const uint32_t s = hq_selector(wp);
+  d.cg = hq_prmt_raw(lut_cg, 0x10000000u, s);
+  d.at = hq_prmt_raw(lut_at, 0x00000010u, s);
+  const uint32_t e = hq_prmt_raw(lut_e, 0x474EFF54u, s);
+  d.bad = swm ^ e;
+  return d;
+}
+
 // same as hq_decode2 with the selector's shift-add issued as one IMAD.HI: p20 must be 2^20, passed through a
 // kernel argument so that the compiler cannot turn it back into LEA.HI (ALU pipe)
 HQ_HDI hq_dec2_t hq_decode2_fma(uint32_t swm, uint32_t p20) {
