@@ -206,10 +206,127 @@ __global__ void __launch_bounds__(256) hq_compact_copy(hq_kargs a, hq_compact_bu
   if (gtid == 0) b.out_idx[n] = tot.x + tot.y;
 }
 
+
+// pass 4, tiled form (reads up to CT_SPAN bytes): DESTINATION-chunk ownership.  A CTA takes a tile of consecutive
+// input reads.  Their source bytes are one contiguous span of the batch, copied into shared memory with aligned
+// 16-byte loads; their output is two contiguous spans (the passed reads of the tile, and its failed reads behind
+// all passed reads of the batch).  Every thread then builds whole aligned 16-byte chunks of the OUTPUT: it finds the
+// read that holds the chunk's first byte (binary search over the tile's scan values in shared memory), pulls the
+// bytes from the staged source at that read's phase, and continues into the following read(s) when the chunk
+// straddles a boundary.  Global stores are full aligned 16-byte chunks except at the two ends of each span.
+constexpr uint32_t CT_RPT = 128;      // reads per tile at most
+constexpr uint32_t CT_SPAN = 23000;   // staged source bytes per array at most (keeps the CTA under 48 KB)
+constexpr uint32_t CT_PAD = 16;       // staged data starts 16 bytes in: a chunk may begin before its read
+
+struct ct_hdr {
+  uint32_t key[2][CT_RPT + 1];  // output offset of read r in the passed / failed stream (tile-local exclusive scan)
+  uint32_t soff[CT_RPT + 1];    // staged offset of the first (trimmed) byte of read r
+};
+
+// bytes [sh, sh + 16) of the 32 bytes A:B, sh in [0, 16), branch-free
+__device__ __forceinline__ uint4 shift_sel(const uint4 &A, const uint4 &B, uint32_t sh) {
+  const bool o1 = (sh & 4u) != 0u, o2 = (sh & 8u) != 0u;
+  const uint32_t t0 = o1 ? A.y : A.x, t1 = o1 ? A.z : A.y, t2 = o1 ? A.w : A.z, t3 = o1 ? B.x : A.w;
+  const uint32_t t4 = o1 ? B.y : B.x, t5 = o1 ? B.z : B.y, t6 = o1 ? B.w : B.z;
+  const uint32_t u0 = o2 ? t2 : t0, u1 = o2 ? t3 : t1, u2 = o2 ? t4 : t2, u3 = o2 ? t5 : t3, u4 = o2 ? t6 : t4;
+  const uint32_t bs = (sh & 3u) * 8u;
+  return make_uint4(__funnelshift_r(u0, u1, bs), __funnelshift_r(u1, u2, bs), __funnelshift_r(u2, u3, bs),
+                    __funnelshift_r(u3, u4, bs));
+}
+
+// 0xFF in every byte j of the 16 with lo <= j < hi, as four words
+__device__ __forceinline__ uint4 range_mask16(uint32_t lo, uint32_t hi) {
+  const uint32_t bits = ((1u << hi) - 1u) & ~((1u << lo) - 1u);  // hi <= 16
+  auto ex = [](uint32_t nib) { return (((nib & 0xFu) * 0x00204081u) & 0x01010101u) * 0xFFu; };
+  return make_uint4(ex(bits), ex(bits >> 4), ex(bits >> 8), ex(bits >> 12));
+}
+
+__global__ void __launch_bounds__(256) hq_compact_copy_tile(hq_kargs a, hq_compact_bufs b, uint32_t rpt, uint32_t cap) {
+  extern __shared__ __align__(16) uint8_t ct_raw[];
+  ct_hdr &h = *reinterpret_cast<ct_hdr *>(ct_raw);
+  constexpr uint32_t HDR = (sizeof(ct_hdr) + 15u) & ~15u;
+  uint8_t *sseq = ct_raw + HDR, *squal = sseq + cap;
+  const uint32_t tid = threadIdx.x, n = a.n_reads;
+  const uint4 tot = b.scan[n];
+  for (uint32_t i0 = blockIdx.x * rpt; i0 < n; i0 += gridDim.x * rpt) {
+    const uint32_t i1 = min(n, i0 + rpt), nt = i1 - i0;
+    __syncthreads();  // the previous tile's staged bytes are no longer read
+    const uint32_t S0a = a.idx[i0] & ~15u, S1 = a.idx[i1];
+    for (uint32_t r = tid; r <= nt; r += 256u) {
+      const uint32_t i = i0 + r;
+      const uint4 sc = b.scan[i];
+      h.key[0][r] = sc.x;
+      h.key[1][r] = tot.x + sc.y;
+      if (r < nt) {
+        const bool pass = a.mask ? (a.mask[i] != 0) : true;
+        const uint32_t st = a.trim ? a.trim[i].start : 0u;
+        const uint32_t slot = pass ? sc.z : tot.z + sc.w;
+        b.out_src[slot] = i;
+        b.out_idx[slot] = pass ? sc.x : tot.x + sc.y;
+        h.soff[r] = a.idx[i] + st - S0a + CT_PAD;
+      }
+    }
+    const uint32_t nb16 = (S1 - S0a + 15u) >> 4;
+    for (uint32_t c = tid; c < nb16; c += 256u) {
+      reinterpret_cast<uint4 *>(sseq + CT_PAD)[c] = __ldg(reinterpret_cast<const uint4 *>(a.seq + S0a) + c);
+      reinterpret_cast<uint4 *>(squal + CT_PAD)[c] = __ldg(reinterpret_cast<const uint4 *>(a.qual + S0a) + c);
+    }
+    __syncthreads();
+#pragma unroll 1
+    for (int stream = 0; stream < 2; ++stream) {
+      const uint32_t *key = h.key[stream];
+      const uint32_t D0 = key[0], D1 = key[nt];
+      if (D1 == D0) continue;
+      const uint32_t c_hi = (D1 + 15u) >> 4;
+      for (uint32_t c = (D0 >> 4) + tid; c < c_hi; c += 256u) {
+        const uint32_t dc = c << 4, d0 = max(dc, D0), d1 = min(dc + 16u, D1);
+        uint32_t lo = 0, hi = nt;  // key[lo] <= d0 < key[hi]
+        while (hi - lo > 1u) {
+          const uint32_t mid = (lo + hi) >> 1;
+          if (key[mid] <= d0) lo = mid; else hi = mid;
+        }
+        uint32_t r = lo, d = d0;
+        uint4 vs = make_uint4(0, 0, 0, 0), vq = vs;
+        while (d < d1) {
+          uint32_t kend = key[r + 1];
+          while (kend <= d) kend = key[++r + 1];  // reads of the other stream and empty reads
+          const uint32_t e = min(d1, kend);
+          const uint32_t x = h.soff[r] + (dc - key[r]);  // staged byte that lands on byte 0 of the chunk (mod 2^32)
+          const uint32_t xa = x & ~15u, sh = x & 15u;
+          const uint4 As = *reinterpret_cast<const uint4 *>(sseq + xa), Bs = *reinterpret_cast<const uint4 *>(sseq + xa + 16u);
+          const uint4 Aq = *reinterpret_cast<const uint4 *>(squal + xa), Bq = *reinterpret_cast<const uint4 *>(squal + xa + 16u);
+          const uint4 ps = shift_sel(As, Bs, sh), pq = shift_sel(Aq, Bq, sh);
+          if (e - d == 16u) {
+            vs = ps;
+            vq = pq;
+          } else {
+            const uint4 m = range_mask16(d - dc, e - dc);
+            vs.x |= ps.x & m.x; vs.y |= ps.y & m.y; vs.z |= ps.z & m.z; vs.w |= ps.w & m.w;
+            vq.x |= pq.x & m.x; vq.y |= pq.y & m.y; vq.z |= pq.z & m.z; vq.w |= pq.w & m.w;
+          }
+          d = e;
+          ++r;
+        }
+        if (d1 - d0 == 16u) {
+          *reinterpret_cast<uint4 *>(b.out_seq + dc) = vs;
+          *reinterpret_cast<uint4 *>(b.out_qual + dc) = vq;
+        } else {  // first / last chunk of the span: its other bytes belong to a neighbouring tile
+          const uint32_t ws[4] = {vs.x, vs.y, vs.z, vs.w}, wq[4] = {vq.x, vq.y, vq.z, vq.w};
+          for (uint32_t t = d0 - dc; t < d1 - dc; ++t) {
+            b.out_seq[dc + t] = (uint8_t)(ws[t >> 2] >> (8u * (t & 3u)));
+            b.out_qual[dc + t] = (uint8_t)(wq[t >> 2] >> (8u * (t & 3u)));
+          }
+        }
+      }
+    }
+  }
+  if (blockIdx.x == 0 && tid == 0) b.out_idx[n] = tot.x + tot.y;
+}
+
 } // namespace
 
-cudaError_t hq_launch_compact(const hq_kargs &a, const hq_compact_bufs &b, uint32_t mean_len, cudaStream_t st,
-                              uint64_t *launches) {
+cudaError_t hq_launch_compact(const hq_kargs &a, const hq_compact_bufs &b, uint32_t mean_len, uint32_t max_len,
+                              cudaStream_t st, uint64_t *launches) {
   const uint32_t n1 = a.n_reads + 1u;
   const uint32_t nb = (n1 + SCAN_THREADS * SCAN_ITEMS - 1u) / (SCAN_THREADS * SCAN_ITEMS);
   hq_compact_sums<<<nb, SCAN_THREADS, 0, st>>>(a, b.block_sums);
@@ -219,6 +336,17 @@ cudaError_t hq_launch_compact(const hq_kargs &a, const hq_compact_bufs &b, uint3
   if (a.n_reads) {
     // lanes per read from the mean read length of the batch (bytes / reads are known to the caller only as
     // capacities, so use the idx span): short reads take 8 or 16 lanes, long reads a whole warp
+    if (max_len && max_len <= CT_SPAN) {
+      uint32_t rpt = CT_SPAN / max_len;
+      if (rpt > CT_RPT) rpt = CT_RPT;
+      const uint32_t cap = ((rpt * max_len + 15u) & ~15u) + 64u;  // + pad in front, + the B half behind the span
+      const uint32_t smem = ((uint32_t)sizeof(ct_hdr) + 15u & ~15u) + 2u * cap;
+      uint32_t tiles = (a.n_reads + rpt - 1u) / rpt;
+      if (tiles > 148u * 8u) tiles = 148u * 8u;
+      hq_compact_copy_tile<<<tiles, 256, smem, st>>>(a, b, rpt, cap);
+      ++*launches;
+      return cudaGetLastError();
+    }
     const int G = mean_len <= 112u ? 8 : mean_len <= 400u ? 16 : 32;
     const uint32_t rpb = 256u / (uint32_t)G;
     uint32_t blocks = (a.n_reads + rpb - 1u) / rpb;

@@ -65,8 +65,8 @@ struct hq_compact_bufs {
   uint32_t *out_idx, *out_src; // n+1 / n
   uint32_t *totals;            // [0]=n_passed [1]=n_failed [2]=passed_bytes [3]=failed_bytes (device)
 };
-cudaError_t hq_launch_compact(const hq_kargs &a, const hq_compact_bufs &b, uint32_t mean_len, cudaStream_t st,
-                              uint64_t *launches);
+cudaError_t hq_launch_compact(const hq_kargs &a, const hq_compact_bufs &b, uint32_t mean_len, uint32_t max_len,
+                              cudaStream_t st, uint64_t *launches);
 
 cudaError_t hq_launch_synth(const hpgq_synth_cfg_t &cfg, uint64_t first_read, uint32_t n, uint8_t *d_seq,
                             uint8_t *d_qual, const uint32_t *d_idx, cudaStream_t st, uint64_t *launches);

@@ -282,3 +282,22 @@ def test_edit_group_kernel_all_lane_widths(q, ob, lmax):
     cp = ob.compact(seq, qual, idx, emask, etrim)
     for k in ("out_idx", "out_src", "out_seq", "out_qual"):
         assert np.array_equal(res[k], cp[k]), k
+
+
+@pytest.mark.parametrize("variant", [0, 1])
+def test_committed_golden_fixture(q, variant):
+    """The CUDA path against tests/golden/oracle_golden.json directly (no oracle in the loop): the section sums and
+    position-weighted checksums committed by tests/golden/make_golden.py."""
+    import json
+    import os
+    with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "oracle_golden.json")) as f:
+        g = json.load(f)
+    seq, qual, idx = q.synth_host(q.synth_cfg(100), 0, g["n"])
+    par = q.make_params(q.WORK_STATS | q.WORK_FILTER | q.WORK_KMERS | q.WORK_CHAOS, k2=7, cg_k=6,
+                        kernel_variant=variant, filter=dict(min_read_length=50, min_read_quality=20, max_N=5))
+    got, res, lay, _ = run_gpu(q, par, seq, qual, idx, 128, kmers=True, k2=7, cg_k=6)
+    assert int(res["mask"].sum()) == g["n_passed"]
+    for name, (s, wsum) in g["sections"].items():
+        sec = lay.section(got, name).astype(object)
+        assert int(sum(sec)) == s, name
+        assert int(sum((i + 1) * int(v) for i, v in enumerate(sec)) % (1 << 61)) == wsum, name
