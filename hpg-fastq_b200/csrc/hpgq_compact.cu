@@ -277,35 +277,68 @@ __global__ void __launch_bounds__(256) hq_compact_copy_tile(hq_kargs a, hq_compa
       const uint32_t *key = h.key[stream];
       const uint32_t D0 = key[0], D1 = key[nt];
       if (D1 == D0) continue;
-      const uint32_t c_hi = (D1 + 15u) >> 4;
-      for (uint32_t c = (D0 >> 4) + tid; c < c_hi; c += 256u) {
+      // a warp owns a contiguous run of the span's chunks, so the read index only moves forward between its rounds
+      const uint32_t c_lo = D0 >> 4, c_hi = (D1 + 15u) >> 4;
+      const uint32_t per = (c_hi - c_lo + 7u) >> 3;
+      const uint32_t w_lo = c_lo + (tid >> 5) * per, w_hi = min(c_hi, w_lo + per);
+      uint32_t r = 0xFFFFFFFFu;
+      for (uint32_t c = w_lo + (tid & 31u); c < w_hi; c += 32u) {
         const uint32_t dc = c << 4, d0 = max(dc, D0), d1 = min(dc + 16u, D1);
-        uint32_t lo = 0, hi = nt;  // key[lo] <= d0 < key[hi]
-        while (hi - lo > 1u) {
-          const uint32_t mid = (lo + hi) >> 1;
-          if (key[mid] <= d0) lo = mid; else hi = mid;
+        if (r == 0xFFFFFFFFu) {
+          uint32_t lo = 0, hi = nt;  // key[lo] <= d0 < key[hi]
+          while (hi - lo > 1u) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if (key[mid] <= d0) lo = mid; else hi = mid;
+          }
+          r = lo;
         }
-        uint32_t r = lo, d = d0;
-        uint4 vs = make_uint4(0, 0, 0, 0), vq = vs;
-        while (d < d1) {
-          uint32_t kend = key[r + 1];
-          while (kend <= d) kend = key[++r + 1];  // reads of the other stream and empty reads
-          const uint32_t e = min(d1, kend);
-          const uint32_t x = h.soff[r] + (dc - key[r]);  // staged byte that lands on byte 0 of the chunk (mod 2^32)
-          const uint32_t xa = x & ~15u, sh = x & 15u;
+        uint32_t kend = key[r + 1];
+        while (kend <= d0) kend = key[++r + 1];  // forward to the read that holds byte d0
+        // first source: read r; second source: the next non-empty read of this stream when the chunk straddles
+        const uint32_t e1 = min(d1, kend);
+        const uint32_t x1 = h.soff[r] + (dc - key[r]);  // staged byte that lands on byte 0 of the chunk (mod 2^32)
+        uint32_t x2 = x1, e2 = d1, r2 = r;
+        if (e1 < d1) {
+          r2 = r + 1u;
+          uint32_t k2 = key[r2 + 1];
+          while (k2 <= e1) k2 = key[++r2 + 1];
+          x2 = h.soff[r2] + (dc - key[r2]);
+          e2 = min(d1, k2);
+        }
+        uint4 vs, vq;
+        {
+          const uint32_t xa = x1 & ~15u, xb = x2 & ~15u;
           const uint4 As = *reinterpret_cast<const uint4 *>(sseq + xa), Bs = *reinterpret_cast<const uint4 *>(sseq + xa + 16u);
           const uint4 Aq = *reinterpret_cast<const uint4 *>(squal + xa), Bq = *reinterpret_cast<const uint4 *>(squal + xa + 16u);
-          const uint4 ps = shift_sel(As, Bs, sh), pq = shift_sel(Aq, Bq, sh);
-          if (e - d == 16u) {
-            vs = ps;
-            vq = pq;
-          } else {
+          const uint4 Cs = *reinterpret_cast<const uint4 *>(sseq + xb), Ds = *reinterpret_cast<const uint4 *>(sseq + xb + 16u);
+          const uint4 Cq = *reinterpret_cast<const uint4 *>(squal + xb), Dq = *reinterpret_cast<const uint4 *>(squal + xb + 16u);
+          const uint4 ps = shift_sel(As, Bs, x1 & 15u), pq = shift_sel(Aq, Bq, x1 & 15u);
+          const uint4 ts = shift_sel(Cs, Ds, x2 & 15u), tq = shift_sel(Cq, Dq, x2 & 15u);
+          const uint4 m = range_mask16(0u, e1 - dc);  // bytes of the first source
+          vs = make_uint4((ps.x & m.x) | (ts.x & ~m.x), (ps.y & m.y) | (ts.y & ~m.y), (ps.z & m.z) | (ts.z & ~m.z),
+                          (ps.w & m.w) | (ts.w & ~m.w));
+          vq = make_uint4((pq.x & m.x) | (tq.x & ~m.x), (pq.y & m.y) | (tq.y & ~m.y), (pq.z & m.z) | (tq.z & ~m.z),
+                          (pq.w & m.w) | (tq.w & ~m.w));
+        }
+        if (__builtin_expect(e2 < d1, 0)) {  // three or more reads in one chunk (reads shorter than 16 bytes)
+          uint32_t d = e2, rr = r2 + 1u;
+          while (d < d1) {
+            uint32_t k3 = key[rr + 1];
+            while (k3 <= d) k3 = key[++rr + 1];
+            const uint32_t e = min(d1, k3);
+            const uint32_t x = h.soff[rr] + (dc - key[rr]);
+            const uint32_t xa = x & ~15u;
+            const uint4 As = *reinterpret_cast<const uint4 *>(sseq + xa), Bs = *reinterpret_cast<const uint4 *>(sseq + xa + 16u);
+            const uint4 Aq = *reinterpret_cast<const uint4 *>(squal + xa), Bq = *reinterpret_cast<const uint4 *>(squal + xa + 16u);
+            const uint4 ps = shift_sel(As, Bs, x & 15u), pq = shift_sel(Aq, Bq, x & 15u);
             const uint4 m = range_mask16(d - dc, e - dc);
-            vs.x |= ps.x & m.x; vs.y |= ps.y & m.y; vs.z |= ps.z & m.z; vs.w |= ps.w & m.w;
-            vq.x |= pq.x & m.x; vq.y |= pq.y & m.y; vq.z |= pq.z & m.z; vq.w |= pq.w & m.w;
+            vs.x = (vs.x & ~m.x) | (ps.x & m.x); vs.y = (vs.y & ~m.y) | (ps.y & m.y);
+            vs.z = (vs.z & ~m.z) | (ps.z & m.z); vs.w = (vs.w & ~m.w) | (ps.w & m.w);
+            vq.x = (vq.x & ~m.x) | (pq.x & m.x); vq.y = (vq.y & ~m.y) | (pq.y & m.y);
+            vq.z = (vq.z & ~m.z) | (pq.z & m.z); vq.w = (vq.w & ~m.w) | (pq.w & m.w);
+            d = e;
+            ++rr;
           }
-          d = e;
-          ++r;
         }
         if (d1 - d0 == 16u) {
           *reinterpret_cast<uint4 *>(b.out_seq + dc) = vs;
