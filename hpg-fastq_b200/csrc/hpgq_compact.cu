@@ -215,7 +215,7 @@ __global__ void __launch_bounds__(256) hq_compact_copy(hq_kargs a, hq_compact_bu
 // bytes from the staged source at that read's phase, and continues into the following read(s) when the chunk
 // straddles a boundary.  Global stores are full aligned 16-byte chunks except at the two ends of each span.
 constexpr uint32_t CT_RPT = 128;      // reads per tile at most
-constexpr uint32_t CT_SPAN = 23000;   // staged source bytes per array at most (keeps the CTA under 48 KB)
+constexpr uint32_t CT_SPAN = 22000;   // staged source bytes per array at most (keeps the CTA under 48 KB)
 constexpr uint32_t CT_PAD = 16;       // staged data starts 16 bytes in: a chunk may begin before its read
 
 struct ct_hdr {
@@ -241,17 +241,22 @@ __device__ __forceinline__ uint4 range_mask16(uint32_t lo, uint32_t hi) {
   return make_uint4(ex(bits), ex(bits >> 4), ex(bits >> 8), ex(bits >> 12));
 }
 
+__host__ __device__ constexpr uint32_t ct_rmap_bytes(uint32_t cap) { return ((cap >> 4) + 8u + 15u) & ~15u; }
+
 __global__ void __launch_bounds__(256) hq_compact_copy_tile(hq_kargs a, hq_compact_bufs b, uint32_t rpt, uint32_t cap) {
   extern __shared__ __align__(16) uint8_t ct_raw[];
   ct_hdr &h = *reinterpret_cast<ct_hdr *>(ct_raw);
   constexpr uint32_t HDR = (sizeof(ct_hdr) + 15u) & ~15u;
-  uint8_t *sseq = ct_raw + HDR, *squal = sseq + cap;
+  uint8_t *rmap = ct_raw + HDR;  // per output chunk of the tile (passed span, then failed span): the read holding its first byte
+  uint8_t *sseq = rmap + ct_rmap_bytes(cap), *squal = sseq + cap;
   const uint32_t tid = threadIdx.x, n = a.n_reads;
   const uint4 tot = b.scan[n];
   for (uint32_t i0 = blockIdx.x * rpt; i0 < n; i0 += gridDim.x * rpt) {
     const uint32_t i1 = min(n, i0 + rpt), nt = i1 - i0;
     __syncthreads();  // the previous tile's staged bytes are no longer read
     const uint32_t S0a = a.idx[i0] & ~15u, S1 = a.idx[i1];
+    const uint4 sc0 = b.scan[i0], sc1 = b.scan[i1];
+    const uint32_t mo_f = ((sc1.x + 15u) >> 4) - (sc0.x >> 4) + 1u;  // the failed span's chunks follow the passed span's
     for (uint32_t r = tid; r <= nt; r += 256u) {
       const uint32_t i = i0 + r;
       const uint4 sc = b.scan[i];
@@ -264,6 +269,16 @@ __global__ void __launch_bounds__(256) hq_compact_copy_tile(hq_kargs a, hq_compa
         b.out_src[slot] = i;
         b.out_idx[slot] = pass ? sc.x : tot.x + sc.y;
         h.soff[r] = a.idx[i] + st - S0a + CT_PAD;
+        // chunk -> read map: this read owns the chunks whose first in-span byte it holds
+        const uint4 scn = b.scan[i + 1u];
+        const uint32_t k0 = pass ? sc.x : tot.x + sc.y, k1 = pass ? scn.x : tot.x + scn.y;
+        const uint32_t D0s = pass ? sc0.x : tot.x + sc0.y;
+        if (k1 > k0) {
+          const uint32_t cb = D0s >> 4;
+          const uint32_t cf = k0 == D0s ? cb : (k0 + 15u) >> 4, cl = (k1 - 1u) >> 4;
+          uint8_t *mp = rmap + (pass ? 0u : mo_f) - cb;
+          for (uint32_t c = cf; c <= cl; ++c) mp[c] = (uint8_t)r;
+        }
       }
     }
     const uint32_t nb16 = (S1 - S0a + 15u) >> 4;
@@ -281,27 +296,23 @@ __global__ void __launch_bounds__(256) hq_compact_copy_tile(hq_kargs a, hq_compa
       const uint32_t c_lo = D0 >> 4, c_hi = (D1 + 15u) >> 4;
       const uint32_t per = (c_hi - c_lo + 7u) >> 3;
       const uint32_t w_lo = c_lo + (tid >> 5) * per, w_hi = min(c_hi, w_lo + per);
-      uint32_t r = 0xFFFFFFFFu;
+      const uint8_t *mp = rmap + (stream ? mo_f : 0u) - c_lo;
       for (uint32_t c = w_lo + (tid & 31u); c < w_hi; c += 32u) {
         const uint32_t dc = c << 4, d0 = max(dc, D0), d1 = min(dc + 16u, D1);
-        if (r == 0xFFFFFFFFu) {
-          uint32_t lo = 0, hi = nt;  // key[lo] <= d0 < key[hi]
-          while (hi - lo > 1u) {
-            const uint32_t mid = (lo + hi) >> 1;
-            if (key[mid] <= d0) lo = mid; else hi = mid;
-          }
-          r = lo;
-        }
-        uint32_t kend = key[r + 1];
-        while (kend <= d0) kend = key[++r + 1];  // forward to the read that holds byte d0
+        const uint32_t r = mp[c];
+        const uint32_t kend = key[r + 1];
         // first source: read r; second source: the next non-empty read of this stream when the chunk straddles
         const uint32_t e1 = min(d1, kend);
         const uint32_t x1 = h.soff[r] + (dc - key[r]);  // staged byte that lands on byte 0 of the chunk (mod 2^32)
         uint32_t x2 = x1, e2 = d1, r2 = r;
         if (e1 < d1) {
-          r2 = r + 1u;
+          r2 = c + 1u < c_hi ? (uint32_t)mp[c + 1u] : r + 1u;  // usually the owner of the next chunk
           uint32_t k2 = key[r2 + 1];
-          while (k2 <= e1) k2 = key[++r2 + 1];
+          if (__builtin_expect(key[r2] != kend || k2 <= kend, 0)) {  // a read shorter than the rest of this chunk
+            r2 = r + 1u;
+            k2 = key[r2 + 1];
+            while (k2 <= e1) k2 = key[++r2 + 1];
+          }
           x2 = h.soff[r2] + (dc - key[r2]);
           e2 = min(d1, k2);
         }
@@ -345,9 +356,21 @@ __global__ void __launch_bounds__(256) hq_compact_copy_tile(hq_kargs a, hq_compa
           *reinterpret_cast<uint4 *>(b.out_qual + dc) = vq;
         } else {  // first / last chunk of the span: its other bytes belong to a neighbouring tile
           const uint32_t ws[4] = {vs.x, vs.y, vs.z, vs.w}, wq[4] = {vq.x, vq.y, vq.z, vq.w};
-          for (uint32_t t = d0 - dc; t < d1 - dc; ++t) {
-            b.out_seq[dc + t] = (uint8_t)(ws[t >> 2] >> (8u * (t & 3u)));
-            b.out_qual[dc + t] = (uint8_t)(wq[t >> 2] >> (8u * (t & 3u)));
+          const uint32_t vlo = d0 - dc, vhi = d1 - dc;
+#pragma unroll
+          for (int w = 0; w < 4; ++w) {
+            const uint32_t w0 = 4u * w;
+            if (vlo <= w0 && vhi >= w0 + 4u) {
+              *reinterpret_cast<uint32_t *>(b.out_seq + dc + w0) = ws[w];
+              *reinterpret_cast<uint32_t *>(b.out_qual + dc + w0) = wq[w];
+            } else if (vlo < w0 + 4u && vhi > w0) {
+#pragma unroll
+              for (int t = 0; t < 4; ++t)
+                if (w0 + t >= vlo && w0 + t < vhi) {
+                  b.out_seq[dc + w0 + t] = (uint8_t)(ws[w] >> (8 * t));
+                  b.out_qual[dc + w0 + t] = (uint8_t)(wq[w] >> (8 * t));
+                }
+            }
           }
         }
       }
@@ -373,7 +396,7 @@ cudaError_t hq_launch_compact(const hq_kargs &a, const hq_compact_bufs &b, uint3
       uint32_t rpt = CT_SPAN / max_len;
       if (rpt > CT_RPT) rpt = CT_RPT;
       const uint32_t cap = ((rpt * max_len + 15u) & ~15u) + 64u;  // + pad in front, + the B half behind the span
-      const uint32_t smem = ((uint32_t)sizeof(ct_hdr) + 15u & ~15u) + 2u * cap;
+      const uint32_t smem = (((uint32_t)sizeof(ct_hdr) + 15u) & ~15u) + ct_rmap_bytes(cap) + 2u * cap;
       uint32_t tiles = (a.n_reads + rpt - 1u) / rpt;
       if (tiles > 148u * 8u) tiles = 148u * 8u;
       hq_compact_copy_tile<<<tiles, 256, smem, st>>>(a, b, rpt, cap);
