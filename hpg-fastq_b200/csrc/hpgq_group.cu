@@ -233,7 +233,9 @@ __device__ __forceinline__ bool mean_ok32(uint32_t S, uint32_t w, int32_t lo, in
   return (int32_t)S >= lo * (int32_t)w && (int32_t)S <= hi * (int32_t)w;
 }
 
-template <int G>
+// GCS: the GC count is needed (statistics); OOQ: the out-of-quality count can fail a read (max_ooq below the
+// longest read this kernel takes)
+template <int G, bool GCS, bool OOQ>
 __global__ void __launch_bounds__(256) hq_qc_regs_kernel(hq_kargs a) {
   constexpr uint32_t NG = 32u / G;
   constexpr int U = 2;
@@ -276,7 +278,7 @@ __global__ void __launch_bounds__(256) hq_qc_regs_kernel(hq_kargs a) {
       const uint32_t r = rr[u], o = oo[u];
       const bool live = r < a.n_reads;
       uint32_t start = 0, len = LL[u];
-      rg_clip(d[u], o, o + len);
+      // the windows below mask their own byte range, so ONE clip (to the kept range) is enough
       if (do_edit) {
         bool edited = false;
         if (a.e_ll > 0) {
@@ -298,8 +300,8 @@ __global__ void __launch_bounds__(256) hq_qc_regs_kernel(hq_kargs a) {
           }
         }
         n_edit += (edited && lig == 0);
-        if (edited) rg_clip(d[u], o + start, o + start + len);
       }
+      rg_clip(d[u], o + start, o + start + len);
       if (a.trim && live && lig == 0) a.trim[r] = hpgq_trim_t{start, len};
       const uint32_t b0 = o + start, b1 = b0 + len;
       // main sums over the registers (bytes outside [b0, b1) are zero)
@@ -309,12 +311,14 @@ __global__ void __launch_bounds__(256) hq_qc_regs_kernel(hq_kargs a) {
         const uint32_t qw = d[u].q[j], sw = d[u].s[j];
         S = __dp4a(qw, 0x01010101u, S);
         fN += rg_zero_flags(sw ^ 0x4E4E4E4Eu) >> 7;
-        fGC += rg_zero_flags((sw & 0xFBFBFBFBu) ^ 0x43434343u) >> 7;  // 'C' = 0x43, 'G' = 0x47
-        fO += (~((qw + a.c_lo) & ~(qw + a.c_hi)) & 0x80808080u) >> 7;
-        hib |= qw;
+        if (GCS) fGC += rg_zero_flags((sw & 0xFBFBFBFBu) ^ 0x43434343u) >> 7;  // 'C' = 0x43, 'G' = 0x47
+        if (OOQ) {
+          fO += (~((qw + a.c_lo) & ~(qw + a.c_hi)) & 0x80808080u) >> 7;
+          hib |= qw;
+        }
       }
       uint32_t nN = __dp4a(fN, 0x01010101u, 0u), nGC = __dp4a(fGC, 0x01010101u, 0u), ooq = __dp4a(fO, 0x01010101u, 0u);
-      if (zero_is_ooq) {  // remove the lane's zeroed bytes from the out-of-range count
+      if (OOQ && zero_is_ooq) {  // remove the lane's zeroed bytes from the out-of-range count
         const uint32_t lo = max(b0, d[u].c), hi = min(b1, d[u].c + RG_LB);
         ooq -= RG_LB - (hi > lo ? hi - lo : 0u);
       }
@@ -330,7 +334,7 @@ __global__ void __launch_bounds__(256) hq_qc_regs_kernel(hq_kargs a) {
       // len < 32*G <= 1024: S < 2^18, counts < 2^10 -> two packed shuffle chains
       uint32_t p1 = S | (nN << 20), p2 = nGC | (ooq << 16);
       p1 = group_sum<G>(p1);
-      p2 = group_sum<G>(p2);
+      if (GCS || OOQ) p2 = group_sum<G>(p2);
       S = p1 & 0xFFFFFu;
       nN = p1 >> 20;
       nGC = p2 & 0xFFFFu;
@@ -609,12 +613,22 @@ cudaError_t hq_launch_qc_group(const hq_kargs &a, uint32_t max_len_in_batch, int
   const uint32_t cap = (uint32_t)sm_count * 8u * 4u;
   if (blocks > cap) blocks = cap;
   if (regs) {
+    const bool gcs = (a.work & HPGQ_WORK_STATS) != 0;
+    const bool ooq = (a.work & HPGQ_WORK_FILTER) != 0 && a.max_ooq < 32 * RG_LB;  // else no read here can exceed it
+#define HQ_REGS(GG)                                                                          \
+  do {                                                                                       \
+    if (gcs && ooq) hq_qc_regs_kernel<GG, true, true><<<blocks, 256, 0, st>>>(a);            \
+    else if (gcs) hq_qc_regs_kernel<GG, true, false><<<blocks, 256, 0, st>>>(a);             \
+    else if (ooq) hq_qc_regs_kernel<GG, false, true><<<blocks, 256, 0, st>>>(a);             \
+    else hq_qc_regs_kernel<GG, false, false><<<blocks, 256, 0, st>>>(a);                     \
+  } while (0)
     switch (G) {
-      case 4: hq_qc_regs_kernel<4><<<blocks, 256, 0, st>>>(a); break;
-      case 8: hq_qc_regs_kernel<8><<<blocks, 256, 0, st>>>(a); break;
-      case 16: hq_qc_regs_kernel<16><<<blocks, 256, 0, st>>>(a); break;
-      default: hq_qc_regs_kernel<32><<<blocks, 256, 0, st>>>(a); break;
+      case 4: HQ_REGS(4); break;
+      case 8: HQ_REGS(8); break;
+      case 16: HQ_REGS(16); break;
+      default: HQ_REGS(32); break;
     }
+#undef HQ_REGS
   } else {
     hq_qc_group_kernel<32><<<blocks, 256, 0, st>>>(a);
   }
