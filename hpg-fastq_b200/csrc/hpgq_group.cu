@@ -519,7 +519,19 @@ __global__ void __launch_bounds__(POS_THREADS, 2) hq_pos_kernel(hq_kargs a, uint
     for (int i = 0; i < POS_PER; ++i) acc[t][i] = 0u;
   uint32_t pk[5][2] = {{0u, 0u}, {0u, 0u}, {0u, 0u}, {0u, 0u}, {0u, 0u}};  // 8-bit lanes: A C G T N
   uint32_t q16[2][2] = {{0u, 0u}, {0u, 0u}};                               // 16-bit lanes: (byte0, byte2), (byte1, byte3)
-  uint32_t since = 0;
+  uint32_t nb[3][2] = {{0u, 0u}, {0u, 0u}, {0u, 0u}};  // 4-bit lanes (<= 15 reads): C | G << 4, A | T << 4, N
+  uint32_t since = 0, nsince = 0;
+  auto fold_nibbles = [&]() {
+#pragma unroll
+    for (int w = 0; w < 2; ++w) {
+      pk[1][w] += nb[0][w] & 0x0F0F0F0Fu;
+      pk[2][w] += (nb[0][w] >> 4) & 0x0F0F0F0Fu;
+      pk[0][w] += nb[1][w] & 0x0F0F0F0Fu;
+      pk[3][w] += (nb[1][w] >> 4) & 0x0F0F0F0Fu;
+      pk[4][w] += nb[2][w];
+      nb[0][w] = nb[1][w] = nb[2][w] = 0u;
+    }
+  };
 
   if (warp == 0) produce(POS_RB * POS_NS);
   __syncthreads();  // barriers initialised, first descriptors visible
@@ -549,18 +561,38 @@ __global__ void __launch_bounds__(POS_THREADS, 2) hq_pos_kernel(hq_kargs a, uint
         for (int w = 0; w < 2; ++w) {
           const uint32_t m = hq_tail_mask(p + 4u * w, L);
           const uint32_t sw = sv[w] & m, qm = qv[w] & m;  // bytes past the read end become 0x00: no symbol
-          pk[0][w] += rg_zero_flags(sw ^ 0x41414141u) >> 7;
-          pk[1][w] += rg_zero_flags(sw ^ 0x43434343u) >> 7;
-          pk[2][w] += rg_zero_flags(sw ^ 0x47474747u) >> 7;
-          pk[3][w] += rg_zero_flags(sw ^ 0x54545454u) >> 7;
-          pk[4][w] += rg_zero_flags(sw ^ 0x4E4E4E4Eu) >> 7;
+          // four bases per PRMT: the low three bits of a byte select from 8-entry LUTs of 4-bit one-hots (C | G << 4,
+          // A | T << 4, N) and of the expected byte; a word with a byte the LUT does not reproduce (lower case,
+          // IUPAC, ...) is re-done byte by byte
+          const uint32_t sel = hq_selector(hq_prmt(sw, 0u, 0x3120u));
+          uint32_t cgv = hq_prmt_raw(0x01000000u, 0x10000000u, sel);
+          uint32_t atv = hq_prmt_raw(0x00000100u, 0x00000010u, sel);
+          uint32_t nv = hq_prmt_raw(0x00000000u, 0x00010000u, sel);
+          if (__builtin_expect(hq_prmt_raw(0x43FF4100u, 0x474EFF54u, sel) != sw, 0)) {
+            cgv = atv = nv = 0u;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const uint32_t c = (sw >> (8 * i)) & 0xFFu;
+              cgv |= (c == 'C' ? 0x01u : c == 'G' ? 0x10u : 0u) << (8 * i);
+              atv |= (c == 'A' ? 0x01u : c == 'T' ? 0x10u : 0u) << (8 * i);
+              nv |= (c == 'N' ? 0x01u : 0u) << (8 * i);
+            }
+          }
+          nb[0][w] += cgv;
+          nb[1][w] += atv;
+          nb[2][w] += nv;
           q16[0][w] += __byte_perm(qm, 0u, 0x4240u);
           q16[1][w] += __byte_perm(qm, 0u, 0x4341u);
         }
       }
     }
     since += POS_RB;
-    if (since > 255u - POS_RB) {  // widen before an 8-bit (or 16-bit) lane can overflow
+    nsince += POS_RB;
+    if (nsince + POS_RB > 15u) {  // 4-bit lanes -> 8-bit lanes
+      fold_nibbles();
+      nsince = 0;
+    }
+    if (nsince == 0u && since + 15u > 255u) {  // widen before an 8-bit (or 16-bit) lane can overflow
 #pragma unroll
       for (int w = 0; w < 2; ++w) {
 #pragma unroll
@@ -578,6 +610,7 @@ __global__ void __launch_bounds__(POS_THREADS, 2) hq_pos_kernel(hq_kargs a, uint
       since = 0;
     }
   }
+  fold_nibbles();
 #pragma unroll
   for (int w = 0; w < 2; ++w) {
 #pragma unroll

@@ -301,3 +301,17 @@ def test_committed_golden_fixture(q, variant):
         sec = lay.section(got, name).astype(object)
         assert int(sum(sec)) == s, name
         assert int(sum((i + 1) * int(v) for i, v in enumerate(sec)) % (1 << 61)) == wsum, name
+
+
+@pytest.mark.parametrize("ooq", [False, True])
+def test_stats_on_mid_length_reads_register_kernel(q, ob, ooq):
+    """Reads of 641..1009 bp with statistics: too long for the tiled kernel, short enough for the register-resident
+    decision kernel (its GC-counting variants, with and without the out-of-quality count) + the position kernel."""
+    rng = np.random.default_rng(77 + ooq)
+    seq, qual, idx = rand_batch(rng, 3000, 0, 900, p_n=0.02)
+    flt = dict(min_read_length=30, min_read_quality=18, max_N=12)
+    if ooq:
+        flt.update(max_out_of_quality=200, left_length=25, min_left_quality=16)
+    _, _, _, emask, _ = check(q, ob, q.make_params(q.WORK_STATS | q.WORK_FILTER, filter=flt), seq, qual, idx, 960)
+    assert 0 < int(emask.sum()) < len(emask)
+    check(q, ob, q.make_params(q.WORK_STATS), seq, qual, idx, 960)
