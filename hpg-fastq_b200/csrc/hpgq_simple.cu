@@ -340,25 +340,48 @@ __global__ void __launch_bounds__(K5_THREADS, 1) hq_k5pos_kernel(hq_kargs a, uin
     }
     __syncwarp();
     if (L) {
-      const uint32_t ph = (o + p0) & 3u;                       // byte phase of position p0 in the first staged word
+      // Straight-line over the 13 words (52 bases) of the slice: four bases per PRMT (2-bit code LUT + expected-byte
+      // LUT whose mismatch marks N / foreign bytes), a 64-bit validity mask whose five-fold AND gives the windows
+      // to count, and the 10-bit code of each window cut out of two consecutive 8-bit word codes.  Position, cell
+      // half and increment of every update are compile-time constants.
+      const uint32_t ph8 = ((o + p0) & 3u) * 8u;               // byte phase of position p0 in the first staged word
       const uint32_t nb = min(L - p0, (uint32_t)K5_W + 4u);    // bases of this read in the slice
       const uint32_t *row = st + lane * K5_STRIDE;
-      uint32_t code = 0, valid = 0, w = 0;
-      for (uint32_t t = 0; t < nb; ++t) {
-        const uint32_t bi = ph + t;
-        if ((bi & 3u) == 0u || t == 0u) w = row[bi >> 2];
-        const uint32_t c = (w >> (8u * (bi & 3u))) & 0xFFu;
-        const uint32_t h = (c >> 1) & 3u, b2 = h ^ (h >> 1);   // A=0 C=1 G=2 T=3 for the four bases
-        if (((0x54474341u >> (8u * b2)) & 0xFFu) == c) {
-          code = ((code << 2) | b2) & 1023u;
-          valid++;
-          if (valid >= 5u) {
-            const uint32_t wp = t - 4u;                        // window starts at p0 + wp
-            atomicAdd(&sm.tab[code * K5_ROW + (wp >> 1)], (wp & 1u) ? 65536u : 1u);
-          }
-        } else {
-          valid = 0;
-        }
+      constexpr int NW = (K5_W + 4) / 4;                       // 13
+      uint32_t c4[NW];
+      uint32_t ok_lo = 0u, ok_hi = 0u;
+      uint32_t wprev = row[0];
+#pragma unroll
+      for (int j = 0; j < NW; ++j) {
+        const uint32_t wnext = row[j + 1];
+        const uint32_t w = __funnelshift_r(wprev, wnext, ph8);
+        wprev = wnext;
+        const uint32_t sel = hq_selector(hq_prmt(w, 0u, 0x3120u));
+        const uint32_t b2w = hq_prmt_raw(0x01000000u, 0x02000003u, sel);          // A 0, C 1, G 2, T 3
+        const uint32_t x = w ^ hq_prmt_raw(0x43FF41FFu, 0x47FFFF54u, sel);        // zero byte <=> one of A C G T
+        const uint32_t zf = ~(((x & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | x) & 0x80808080u;
+        const uint32_t nib = ((zf >> 7) * 0x10204080u) >> 28;                      // the four flags as one nibble
+        if (j < 8) ok_lo |= nib << (4 * (j & 7));
+        else ok_hi |= nib << (4 * (j & 7));
+        c4[j] = __dp4a(b2w, 0x01041040u, 0u);                                      // b0 b1 b2 b3 -> 8-bit code
+      }
+      // bases beyond the read's share of the slice are not valid
+      if (nb < 32u) {
+        ok_lo &= (1u << nb) - 1u;
+        ok_hi = 0u;
+      } else if (nb < 64u) {
+        ok_hi &= (1u << (nb - 32u)) - 1u;
+      }
+      unsigned long long m5 = ((unsigned long long)ok_hi << 32) | ok_lo;
+      m5 = m5 & (m5 >> 1) & (m5 >> 2) & (m5 >> 3) & (m5 >> 4);                     // bit t: window starting at t
+      const uint32_t m_lo = (uint32_t)m5, m_hi = (uint32_t)(m5 >> 32);
+#pragma unroll
+      for (int t = 0; t < K5_W; ++t) {
+        const int u = t + 4, j = u >> 2, i = u & 3;                                // window ends at base u
+        const uint32_t H = (c4[j - 1] << 8) | c4[j];
+        const uint32_t code = (H >> (6 - 2 * i)) & 1023u;
+        if (((t < 32 ? m_lo : m_hi) >> (t & 31)) & 1u)
+          atomicAdd(&sm.tab[code * K5_ROW + (t >> 1)], (t & 1) ? 65536u : 1u);
       }
     }
     __syncwarp();
