@@ -305,7 +305,7 @@ constexpr int K5_ROW = K5_W / 2 + 1;        // words per 5-mer row, odd: rows of
 
 struct k5_smem {
   uint32_t tab[1024 * K5_ROW];                          // u16 pairs
-  uint32_t stage[K5_THREADS / 32][32 * K5_STRIDE];
+  uint32_t stage[2][K5_THREADS / 32][32 * K5_STRIDE];  // double-buffered: the next group is in flight (cp.async)
 };
 
 __global__ void __launch_bounds__(K5_THREADS, 1) hq_k5pos_kernel(hq_kargs a, uint32_t reads_per_slab) {
@@ -317,28 +317,43 @@ __global__ void __launch_bounds__(K5_THREADS, 1) hq_k5pos_kernel(hq_kargs a, uin
   for (uint32_t i = tid; i < 1024u * K5_ROW; i += K5_THREADS) sm.tab[i] = 0u;
   __syncthreads();
   const uint32_t r_begin = blockIdx.y * reads_per_slab, r_end = min(a.n_reads, r_begin + reads_per_slab);
-  uint32_t *st = sm.stage[warp];
-  for (uint32_t g0 = r_begin + warp * 32u; g0 < r_end; g0 += (K5_THREADS / 32) * 32u) {
-    // my read of the group
+  // my read of group g0: offset and length (0 = nothing to count in this slice)
+  auto describe = [&](uint32_t g0, uint32_t &o, uint32_t &L) {
     const uint32_t r = g0 + lane;
-    uint32_t o = 0, L = 0;
+    o = 0u;
+    L = 0u;
     if (r < r_end) {
       o = a.idx[r];
       L = a.idx[r + 1] - o;
-      if (L > a.Lcap || L < p0 + 5u || (use_mask && !a.mask[r])) L = 0;  // nothing to count in this slice
+      if (L > a.Lcap || L < p0 + 5u || (use_mask && !a.mask[r])) L = 0u;
     }
-    // stage: read i of the group <- lanes 0..K5_SW-1 load consecutive aligned words of its slice
-    const uint32_t any = __ballot_sync(0xFFFFFFFFu, L != 0u);
-    if (!any) continue;
-#pragma unroll 4
+  };
+  // stage: read i of the group <- lanes 0..K5_SW-1 copy consecutive aligned words of its slice (asynchronously)
+  auto stage = [&](uint32_t *buf, uint32_t o, uint32_t L) {
+#pragma unroll 8
     for (int i = 0; i < 32; ++i) {
       const uint32_t oi = __shfl_sync(0xFFFFFFFFu, o, i), Li = __shfl_sync(0xFFFFFFFFu, L, i);
       if (Li == 0u) continue;  // warp-uniform
       const uint32_t first = oi + p0, wa = (first & ~3u) + 4u * lane;
       const uint32_t last = oi + min(Li, p0 + (uint32_t)K5_W + 4u);  // one past the last byte needed
-      if (lane < (uint32_t)K5_SW && wa < last) st[i * K5_STRIDE + lane] = __ldg(reinterpret_cast<const uint32_t *>(a.seq + wa));
+      if (lane < (uint32_t)K5_SW && wa < last)
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(hq_smem_u32(buf + i * K5_STRIDE + lane)), "l"(a.seq + wa) : "memory");
     }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  constexpr uint32_t GSTEP = (K5_THREADS / 32) * 32u;
+  uint32_t g0 = r_begin + warp * 32u, cur = 0u, o = 0u, L = 0u;
+  if (g0 < r_end) {
+    describe(g0, o, L);
+    stage(sm.stage[0][warp], o, L);
+  }
+  for (; g0 < r_end; g0 += GSTEP) {
+    uint32_t on = 0u, Ln = 0u;
+    describe(g0 + GSTEP, on, Ln);             // past r_end: all lanes get L = 0, an empty copy group
+    stage(sm.stage[cur ^ 1u][warp], on, Ln);
+    asm volatile("cp.async.wait_group 1;" ::: "memory");
     __syncwarp();
+    const uint32_t *st = sm.stage[cur][warp];
     if (L) {
       // Straight-line over the 13 words (52 bases) of the slice: four bases per PRMT (2-bit code LUT + expected-byte
       // LUT whose mismatch marks N / foreign bytes), a 64-bit validity mask whose five-fold AND gives the windows
@@ -385,7 +400,11 @@ __global__ void __launch_bounds__(K5_THREADS, 1) hq_k5pos_kernel(hq_kargs a, uin
       }
     }
     __syncwarp();
+    o = on;
+    L = Ln;
+    cur ^= 1u;
   }
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
   __syncthreads();
   unsigned long long *C = a.ctr;
   for (uint32_t i = tid; i < 1024u * K5_ROW; i += K5_THREADS) {
