@@ -26,17 +26,35 @@
 namespace hqt {
 
 constexpr int NSMAX = 8;                 // pipeline stages are a launch parameter (hq_kargs.n_stages <= NSMAX)
-#ifndef HQ_NCW
-#define HQ_NCW 15
+// Developer A/B switches of the ring (both off by default).
+// HQ_NOPROD = 1: no producer warp.  All 16 warps consume (4 per SM sub-partition, so the four schedulers carry the
+// same load); the warp that is LAST to finish a tile refills its ring stage, and the two boundary offsets that
+// refill needs travel with the stage's previous load, so nobody spins or waits on a global load.
+// HQ_NOPROD = 0: 15 consumer warps + 1 producer warp polling the `empty` barriers (the earlier design, kept for A/B).
+// Measured on B200 (2^23 x 150 bp, K = 5, G = 8): producer warp 3750 GB/s, HQ_NOPROD 3440 GB/s (the warps wait
+// twice as long for a full stage), so the producer warp stays the default.
+#ifndef HQ_NOPROD
+#define HQ_NOPROD 0
 #endif
-constexpr int NCW = HQ_NCW;                 // consumer warps (15 + producer = 4 warps per SM sub-partition: 128 registers each)
-constexpr int THREADS = (NCW + 1) * 32;  // + 1 producer warp
+// HQ_TICKET = 1: the warps of a CTA draw the tile's chunks of NG reads from a per-stage ticket counter instead of
+// owning a fixed share, so they finish a tile together and nobody runs ahead into a stage that is still loading.
+// Measured slower in both designs (3750 -> 3280 GB/s with the producer warp): the draw is on every iteration's path.
+#ifndef HQ_TICKET
+#define HQ_TICKET 0
+#endif
+#ifndef HQ_NCW
+#define HQ_NCW (HQ_NOPROD ? 16 : 15)
+#endif
+constexpr int NCW = HQ_NCW;                 // consumer warps (4 warps per SM sub-partition: 128 registers each)
+constexpr int THREADS = (NCW + (HQ_NOPROD ? 0 : 1)) * 32;
+constexpr uint32_t NB_BYTES = HQ_NOPROD ? 32u : 0u;  // two 16-byte offset chunks at the end of a stage's idx area
 constexpr int TAB = 640;                 // positions held by the block-private tables
 constexpr int KMAX = 5;
 
 // fixed shared-memory carve-up (bytes)
-constexpr uint32_t SM_BAR = 0;                               // full[NSMAX], empty[NSMAX]
-constexpr uint32_t SM_TAB = 128;                             // u32 [6][TAB]: accq, A, C, G, T, other
+constexpr uint32_t SM_BAR = 0;                               // full[NSMAX], empty[NSMAX] (u64), ticket[NSMAX] (u32)
+constexpr uint32_t SM_TICKET = 128;
+constexpr uint32_t SM_TAB = 256;                             // u32 [6][TAB]: accq, A, C, G, T, other
 constexpr uint32_t SM_LEN = SM_TAB + 4u * 6u * TAB;          // u32 [TAB + 4]
 constexpr uint32_t SM_QH = SM_LEN + 4u * (TAB + 4);          // u32 [256]
 constexpr uint32_t SM_GC = SM_QH + 4u * 256u;                // u32 [104]
@@ -47,7 +65,7 @@ constexpr uint32_t SM_STAGES = (SM_RECS + 16u * NCW * 32u + 127u) & ~127u;
 static_assert(SM_SUMQ % 8 == 0, "sumq must be 8-byte aligned");
 static_assert(SM_RECS % 16 == 0, "records must be 16-byte aligned");
 
-__host__ __device__ inline uint32_t idx_cap_bytes(uint32_t RT) { return (((RT + 1u) * 4u + 15u) & ~15u) + 16u; }
+__host__ __device__ inline uint32_t idx_cap_bytes(uint32_t RT) { return (((RT + 1u) * 4u + 15u) & ~15u) + 16u + NB_BYTES; }
 
 template <int K, int G, bool FULL>
 __global__ void __launch_bounds__(THREADS, 1) qc_tiled_kernel(const hq_kargs a);
