@@ -39,7 +39,7 @@ METRIC = "reads/s (stats+filter, 150 bp PE, per-read QC hot path)"
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--reads", type=int, default=100_000_000, help="reads per GPU per step")
@@ -64,7 +64,7 @@ def measured_peak():
 class ClockSampler:
     """Samples SM clock and throttle reasons through NVML from a thread while the timed region runs."""
 
-    def __init__(self, gpu, period=0.01):
+    def __init__(self, gpu, period=0.004):
         import threading
         self.sm, self.reasons, self.mx, self.err = [], set(), None, None
         self._stop = threading.Event()

@@ -30,8 +30,10 @@ uint32_t env_u32(const char *name, uint32_t dflt, uint32_t lo, uint32_t hi) {
 }
 
 bool pick_geom(uint32_t max_len, uint32_t n_reads, int sm_count, size_t smem_limit, hq_geom *out) {
-  const uint32_t NS = env_u32("HPGQ_STAGES", 3, 2, NSMAX);
-  const uint32_t tile_bytes = env_u32("HPGQ_TILE_BYTES", 26 * 1024, 1024, 64 * 1024);
+  // two stages of the largest tiles that fit (300 reads of 150 bp) beat three stages of 180 reads by 2.3 %: the
+  // per-tile entry / exit costs a warp about a fifth of an iteration (profiles/tiled_r1i_summary.md)
+  const uint32_t NS = env_u32("HPGQ_STAGES", 2, 2, NSMAX);
+  const uint32_t tile_bytes = env_u32("HPGQ_TILE_BYTES", 46 * 1000, 1024, 64 * 1024);
   if (max_len == 0) max_len = 1;
   const uint32_t words = (max_len + 3u) / 4u;
   double best = -1.0;
