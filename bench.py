@@ -154,11 +154,31 @@ def run_reference(args):
                                    "submodule absent from its tree, so oracle/_ref holds only its chaos-game code"},
         "e2e": {"value": val, "unit": "reads/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
+
+
+_REAL_STDOUT = None
+
+
+def quiet_stdout():
+    """Everything libraries print to fd 1 (NCCL's version banner, for one) goes to stderr: stdout carries exactly
+    one JSON line, written by emit()."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+
+
+def emit(line):
+    out = _REAL_STDOUT if _REAL_STDOUT is not None else sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
 
 
 def main():
     args = parse()
+    quiet_stdout()
     if args.impl == "reference":
         run_reference(args)
         return
@@ -366,7 +386,7 @@ def main():
             "fastq_gbs": value * BYTES_PER_READ / 1e9,
             "roofline": roofline, "clocks": clocks, "gpu_launches": int(launches), "e2e": e2e, "cpu_baseline": cpu,
         }
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
