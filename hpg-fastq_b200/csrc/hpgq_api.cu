@@ -55,6 +55,12 @@ struct hpgq_slot {
   uint8_t *h_out_seq = nullptr, *h_out_qual = nullptr;
   uint32_t *h_out_idx = nullptr, *h_out_src = nullptr, *h_lens = nullptr;
   uint64_t h_out_bytes = 0, h_out_reads = 0;
+  // FASTQ text path (hpgq_batch_submit_text): device chunk, pinned staging, parser scratch
+  uint8_t *d_text = nullptr, *h_text = nullptr;
+  uint64_t d_text_cap = 0, h_text_cap = 0;
+  hq_parse_bufs pb = {};
+  uint32_t *h_pinfo = nullptr;  // pinned copy of pb.info
+  bool text_batch = false;
 };
 
 struct hpgq_ctx {
@@ -172,6 +178,9 @@ static void slot_free(hpgq_slot &s) {
   cudaFree(s.cb.out_idx); cudaFree(s.cb.out_src); cudaFree(s.cb.totals);
   cudaFreeHost(s.h_out_seq); cudaFreeHost(s.h_out_qual); cudaFreeHost(s.h_out_idx); cudaFreeHost(s.h_out_src);
   cudaFreeHost(s.h_lens);
+  cudaFree(s.d_text); cudaFreeHost(s.h_text); cudaFreeHost(s.h_pinfo);
+  cudaFree(s.pb.tile_cnt); cudaFree(s.pb.cta_sum); cudaFree(s.pb.nl); cudaFree(s.pb.info);
+  cudaFree(s.pb.seq_off); cudaFree(s.pb.qual_off); cudaFree(s.pb.hdr_off); cudaFree(s.pb.hdr_len);
   if (s.ev0) cudaEventDestroy(s.ev0);
   if (s.ev1) cudaEventDestroy(s.ev1);
   if (s.stream) cudaStreamDestroy(s.stream);

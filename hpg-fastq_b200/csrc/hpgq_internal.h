@@ -70,3 +70,23 @@ cudaError_t hq_launch_compact(const hq_kargs &a, const hq_compact_bufs &b, uint3
 
 cudaError_t hq_launch_synth(const hpgq_synth_cfg_t &cfg, uint64_t first_read, uint32_t n, uint8_t *d_seq,
                             uint8_t *d_qual, const uint32_t *d_idx, cudaStream_t st, uint64_t *launches);
+
+// ------------------------------------------------------------------ device FASTQ text parser (hpgq_parse.cu)
+enum { HQ_PINFO_LINES = 0, HQ_PINFO_READS, HQ_PINFO_MAXLEN, HQ_PINFO_BAD, HQ_PINFO_BASES, HQ_PINFO_STATUS, HQ_PINFO_COUNT = 8 };
+// bits of info[HQ_PINFO_STATUS] = hpgq_text_info_t.status (include/hpg_fastq_cuda.h HPGQ_TEXT_*)
+enum { HQ_PSTAT_LINES = 1, HQ_PSTAT_RECORD = 2, HQ_PSTAT_TOO_MANY = 4 };
+struct hq_parse_bufs {
+  const uint8_t *text;  // chunk on the device, 16-byte aligned, readable to n_bytes + 16
+  uint32_t n_bytes;
+  uint32_t *tile_cnt;   // ceil(n_bytes / 16384) + 1
+  uint32_t *cta_sum;    // 8 * sm_count + 1
+  uint32_t *nl;         // cap_lines positions of the line breaks
+  uint32_t cap_lines;
+  uint32_t *info;       // HQ_PINFO_COUNT words
+  uint32_t *seq_off, *qual_off, *hdr_off, *hdr_len;  // cap_reads each
+  uint32_t cap_reads;
+  uint64_t cap_bytes;
+  uint8_t *seq, *qual;  // outputs: the SoA batch
+  uint32_t *idx;
+};
+cudaError_t hq_launch_parse(const hq_parse_bufs &b, int sm_count, cudaStream_t st, uint64_t *launches);

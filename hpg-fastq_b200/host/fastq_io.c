@@ -150,6 +150,46 @@ int hq_reader_next(hq_reader_t *r, hq_host_batch_t *bt) {
   return n ? 1 : 0;
 }
 
+/* start of the line after the one that begins at p, or size if there is none */
+static uint64_t line_after(const hq_reader_t *r, uint64_t p) {
+  if (p >= r->size) return r->size;
+  const uint8_t *nl = (const uint8_t *)memchr(r->data + p, '\n', r->size - p);
+  return nl ? (uint64_t)(nl - r->data) + 1 : r->size;
+}
+
+int hq_reader_peek_text(const hq_reader_t *r, uint64_t max_bytes, uint64_t *off, uint64_t *len) {
+  if (r->pos >= r->size) return 0;
+  *off = r->pos;
+  if (r->size - r->pos <= max_bytes) {
+    *len = r->size - r->pos;
+    return 1;
+  }
+  /* walk back over line starts from pos + max_bytes; a header is the only line that starts with '@' and is
+   * followed, two lines on, by a line that starts with '+' (a quality line may start with '@', but then the line
+   * two further is a sequence) */
+  uint64_t p = r->pos + max_bytes;
+  const uint64_t floor = r->pos + max_bytes / 2;
+  while (p > floor) {
+    const uint8_t *nl = (const uint8_t *)memrchr(r->data + floor, '\n', p - floor);
+    if (!nl) break;
+    const uint64_t ls = (uint64_t)(nl - r->data) + 1;
+    if (ls < r->size && ls <= r->pos + max_bytes && r->data[ls] == '@') {
+      const uint64_t l2 = line_after(r, line_after(r, ls));
+      if (l2 < r->size && r->data[l2] == '+') {
+        *len = ls - r->pos;
+        return 1;
+      }
+    }
+    p = (uint64_t)(nl - r->data);
+  }
+  return -1;
+}
+
+void hq_reader_advance(hq_reader_t *r, uint64_t bytes, uint64_t records) {
+  r->pos += bytes;
+  r->record += records;
+}
+
 /* ------------------------------------------------------------------ writer */
 struct hq_writer {
   int fd;

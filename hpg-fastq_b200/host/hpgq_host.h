@@ -51,6 +51,7 @@ typedef struct hq_options {
   int max_read_len;    /* --max-read-length L: skip the pre-scan that sizes the per-position tables */
   int k2;              /* --kmers2 K: second k-mer size (BASELINE.json: 11), stats only             */
   int cg_k;            /* --chaos-game K: chaos-game word size (old/chaos_game.c), stats only       */
+  int host_parse;      /* --host-parse: records are cut by hq_reader_next, not by the device parser */
 } hq_options_t;
 
 /* Parses argv (argv[0] = command name, as in src/hpg-fastq.c:55-57).  Returns NULL after printing the
@@ -94,6 +95,13 @@ int hq_reader_scan(hq_reader_t *r, uint32_t *max_line, uint64_t *n_lines);
  * < 0 on a malformed record (message in hq_reader_error). */
 int hq_reader_next(hq_reader_t *r, hq_host_batch_t *b);
 const char *hq_reader_error(const hq_reader_t *r);
+/* Device-parse path (hpgq_batch_submit_text): the next run of whole records, at most max_bytes long, as a span of
+ * the mapped file -- nothing is scanned or copied except a short backward search for a record boundary (a line
+ * that starts with '@' whose second successor starts with '+').  Returns 1 and sets *off / *len, 0 at end of
+ * file, -1 when no boundary was found inside the budget (the caller falls back to hq_reader_next).  The reader
+ * does not move until hq_reader_advance. */
+int hq_reader_peek_text(const hq_reader_t *r, uint64_t max_bytes, uint64_t *off, uint64_t *len);
+void hq_reader_advance(hq_reader_t *r, uint64_t bytes, uint64_t records);
 
 /* ------------------------------------------------------------------ FASTQ writer */
 typedef struct hq_writer hq_writer_t;

@@ -1,9 +1,14 @@
 /*
  * main.c -- `hpg-fastq stats|filter|edit`: the reference's command line (src/hpg-fastq.c:38-127) over the
  * B200 C ABI.  The workflow of each command keeps the reference's shape
- *   producer  fastq_*_producer  (src/stats_fastq.c:174-196)  -> hq_reader_next: FASTQ text -> pinned SoA batch
+ *   producer  fastq_*_producer  (src/stats_fastq.c:174-196)  -> hq_reader_peek_text: a span of whole records of the
+ *                                                                mapped file (records are cut on the GPU), or
+ *                                                                hq_reader_next: FASTQ text -> pinned SoA batch
+ *                                                                (--host-parse, and input the device parser
+ *                                                                hands back: blank lines, malformed records)
  *   worker    fastq_*_worker    (src/stats_fastq.c:202-251, src/filter_fastq.c:134-155, src/edit_fastq.c:142-178)
- *                                                             -> hpgq_batch_submit (H2D + kernels, async)
+ *                                                             -> hpgq_batch_submit_text / hpgq_batch_submit
+ *                                                                (H2D + kernels, async)
  *   consumer  fastq_*_consumer  (src/stats_fastq.c:257-417, src/filter_fastq.c:161-176, src/edit_fastq.c:184-208)
  *                                                             -> hpgq_batch_wait + ordered FASTQ writer;
  *                                                                the statistics merge stays on the device
@@ -60,6 +65,10 @@ typedef struct run {
   int busy[HQ_MAX_GPUS][HQ_SLOTS];
   hq_writer_t *w_pass, *w_fail;
   uint64_t num_passed, num_failed, num_edited, num_reads;
+  int device_parse;      /* records are cut on the GPU until a chunk is handed back */
+  uint64_t text_budget;  /* bytes of FASTQ text per device-parsed batch */
+  uint32_t *tmp_off;     /* batch_size header offsets inside a chunk */
+  uint64_t n_text_batches, n_host_batches;
 } run_t;
 
 static int alloc_host_batch(hq_host_batch_t *b, uint32_t cap_reads, uint64_t cap_bytes) {
@@ -124,6 +133,36 @@ static int run_pipeline(run_t *r) {
     const int g = (int)(b % (uint64_t)N), s = (int)((b / (uint64_t)N) % HQ_SLOTS);
     if (r->busy[g][s] && consume(r, g, s)) return 1;
     hq_host_batch_t *hb = &r->hb[g][s];
+    if (r->device_parse) {
+      uint64_t off = 0, len = 0;
+      const int pk = hq_reader_peek_text(r->reader, r->text_budget, &off, &len);
+      if (pk == 0) break;
+      if (pk > 0) {
+        hpgq_text_info_t info;
+        int rc = hpgq_batch_submit_text(r->ctx[g], hq_reader_data(r->reader) + off, len, s, &info);
+        if (rc) return die_hpgq("hpgq_batch_submit_text", rc);
+        if (info.status == 0) {
+          hb->n_reads = info.n_reads;
+          hb->max_len = info.max_len;
+          if (r->o->command != HQ_CMD_STATS) { /* the writer needs the header lines */
+            if ((rc = hpgq_batch_text_headers(r->ctx[g], s, r->tmp_off, hb->hdr_len))) return die_hpgq("hpgq_batch_text_headers", rc);
+            for (uint32_t i = 0; i < info.n_reads; i++) hb->hdr_off[i] = off + r->tmp_off[i];
+          }
+          hq_reader_advance(r->reader, len, info.n_reads);
+          r->busy[g][s] = 1;
+          r->n_text_batches++;
+          continue;
+        }
+        if (info.status == HPGQ_TEXT_TOO_MANY && r->text_budget > (1u << 16)) {
+          r->text_budget /= 2; /* shorter reads than the sizing assumed: same batch again, smaller chunk */
+          b--;
+          continue;
+        }
+      }
+      /* blank lines, a malformed record, no boundary found: the host reader takes over (and owns the messages) */
+      r->device_parse = 0;
+      logf_("INFO", "device FASTQ parser handed the input back to the host reader");
+    }
     int got = hq_reader_next(r->reader, hb);
     if (got < 0) {
       fprintf(stderr, "\nFATAL: %s: %s\n", r->o->in_filename, hq_reader_error(r->reader));
@@ -135,6 +174,7 @@ static int run_pipeline(run_t *r) {
     int rc = hpgq_batch_submit(r->ctx[g], &hbatch, s);
     if (rc) return die_hpgq("hpgq_batch_submit", rc);
     r->busy[g][s] = 1;
+    r->n_host_batches++;
   }
   /* drain in batch order: the oldest outstanding batch is b - N*HQ_SLOTS */
   const uint64_t first = b > (uint64_t)N * HQ_SLOTS ? b - (uint64_t)N * HQ_SLOTS : 0;
@@ -219,6 +259,10 @@ static int run_command(hq_options_t *o) {
         goto out;
       }
   }
+  r->device_parse = !o->host_parse;
+  r->text_budget = 2 * cap_bytes; /* bases are less than half of the text, so a chunk never exceeds cap_bytes bases */
+  r->tmp_off = (uint32_t *)malloc(((size_t)lim.max_reads_per_batch + 1) * sizeof(uint32_t));
+  if (!r->tmp_off) goto out;
   if (o->command == HQ_CMD_FILTER) {
     snprintf(pass_name, sizeof pass_name, "%s/passed.fq", o->out_dirname); /* src/filter_fastq.c:185 */
     snprintf(fail_name, sizeof fail_name, "%s/failed.fq", o->out_dirname); /* src/filter_fastq.c:189 */
@@ -311,8 +355,9 @@ static int run_command(hq_options_t *o) {
   {
     char msg[256];
     const double dt = now_s() - t0;
-    snprintf(msg, sizeof msg, "%s: %lu reads on %d GPU(s) in %.3f s (%.3g reads/s, %s)", o->command_name,
-             (unsigned long)r->num_reads, r->n_gpus, dt, dt > 0 ? (double)r->num_reads / dt : 0.0, hpgq_version());
+    snprintf(msg, sizeof msg, "%s: %lu reads on %d GPU(s) in %.3f s (%.3g reads/s, %lu device-parsed + %lu host-parsed batches, %s)",
+             o->command_name, (unsigned long)r->num_reads, r->n_gpus, dt, dt > 0 ? (double)r->num_reads / dt : 0.0,
+             (unsigned long)r->n_text_batches, (unsigned long)r->n_host_batches, hpgq_version());
     logf_("INFO", msg);
   }
   status = 0;
@@ -324,6 +369,7 @@ out:
     for (int s = 0; s < HQ_SLOTS; s++) free_host_batch(&r->hb[g][s]);
   }
   if (r->reader) hq_reader_close(r->reader);
+  free(r->tmp_off);
   free(r);
   return status;
 }

@@ -47,6 +47,7 @@ static const hq_optdef_t OPTS[] = {
     {NULL, "max-read-length", A_INT, "[B200] longest read to expect (skips the sizing pre-scan)", C_S, 1},
     {NULL, "kmers2", A_INT, "[B200] also count k-mers of this size (eg. 11)", C_S, 1},
     {NULL, "chaos-game", A_INT, "[B200] chaos-game frequency matrices of this word size (eg. 10)", C_S, 1},
+    {NULL, "host-parse", A_LIT, "[B200] cut the FastQ records on the host instead of on the GPU", C_ALL, 1},
 };
 #define N_OPTS ((int)(sizeof OPTS / sizeof OPTS[0]))
 
@@ -141,6 +142,7 @@ static int set_option(hq_options_t *o, int i, const char *val) {
     case 16: o->max_read_len = iv; break;
     case 17: o->k2 = iv; break;
     case 18: o->cg_k = iv; break;
+    case 19: o->host_parse = 1; break;
     default: return 0;
   }
 #undef SETS

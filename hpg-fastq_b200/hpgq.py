@@ -90,11 +90,19 @@ class SynthCfg(C.Structure):
                 ("lowercase_ppm", C.c_uint32), ("reserved", C.c_uint32)]
 
 
+class TextInfo(C.Structure):
+    """hpgq_text_info_t"""
+    _fields_ = [("n_reads", C.c_uint32), ("max_len", C.c_uint32), ("n_bases", C.c_uint64), ("n_lines", C.c_uint32),
+                ("status", C.c_uint32), ("bad_record", C.c_uint32), ("reserved", C.c_uint32)]
+
+
+TEXT_LINES, TEXT_RECORD, TEXT_TOO_MANY = 1, 2, 4
 DEFAULT_SEED = 0x48504751
 
 EXPORTS = [
     "hpgq_strerror", "hpgq_last_error", "hpgq_layout", "hpgq_device_count", "hpgq_ctx_create", "hpgq_ctx_destroy",
     "hpgq_set_params", "hpgq_get_layout", "hpgq_batch_submit", "hpgq_batch_submit_device", "hpgq_batch_wait",
+    "hpgq_batch_submit_text", "hpgq_batch_text_headers",
     "hpgq_batch_sync", "hpgq_batch_device_views", "hpgq_counters_reset", "hpgq_counters_download",
     "hpgq_counters_device_ptr", "hpgq_counters_reduce", "hpgq_counters_finalize_host", "hpgq_slot_stream", "hpgq_launch_count",
     "hpgq_last_kernel_ms", "hpgq_synth_device", "hpgq_synth_host", "hpgq_dev_alloc", "hpgq_dev_free",
@@ -233,6 +241,22 @@ class Ctx:
     def submit_raw(self, n_reads: int, seq_ptr: int, qual_ptr: int, idx_ptr: int, slot: int = 0):
         b = Batch(n_reads, 0, seq_ptr, qual_ptr, idx_ptr)
         _ck(self.lib.hpgq_batch_submit(self.h, C.byref(b), C.c_int(slot)), "hpgq_batch_submit")
+
+    def submit_text(self, text: bytes | np.ndarray, slot: int = 0) -> TextInfo:
+        """FASTQ text chunk -> device parser -> the same work as submit(); info.status != 0: not submitted."""
+        arr = np.frombuffer(text, dtype=np.uint8) if isinstance(text, (bytes, bytearray)) else np.ascontiguousarray(text, dtype=np.uint8)
+        self._keep[slot] = (arr,)
+        info = TextInfo()
+        _ck(self.lib.hpgq_batch_submit_text(self.h, C.c_void_p(arr.ctypes.data), C.c_uint64(arr.size), C.c_int(slot),
+                                            C.byref(info)), "hpgq_batch_submit_text")
+        return info
+
+    def text_headers(self, n_reads: int, slot: int = 0):
+        off = np.zeros(max(n_reads, 1), dtype=np.uint32)
+        ln = np.zeros(max(n_reads, 1), dtype=np.uint32)
+        _ck(self.lib.hpgq_batch_text_headers(self.h, C.c_int(slot), C.c_void_p(off.ctypes.data), C.c_void_p(ln.ctypes.data)),
+            "hpgq_batch_text_headers")
+        return off[:n_reads], ln[:n_reads]
 
     def wait(self, slot: int = 0) -> dict:
         r = Result()

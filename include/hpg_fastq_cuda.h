@@ -197,6 +197,31 @@ int hpgq_batch_submit(hpgq_ctx_t *ctx, const hpgq_batch_t *host_batch, int slot)
 /* Device-resident batch: pointers are device pointers, 16-byte aligned, each array readable
  * 32 bytes past its logical end; idx need not start at 0.  No copies are made. */
 int hpgq_batch_submit_device(hpgq_ctx_t *ctx, const hpgq_batch_t *dev_batch, int slot);
+/* FASTQ text batch: the device-side replacement of the record scan of fastq_fread_se()
+ * (reference call sites src/stats_fastq.c:183, src/filter_fastq.c:114, src/edit_fastq.c:121).  `text` is host memory
+ * (pinned: copied asynchronously; pageable: staged through the slot's pinned buffer) holding n_bytes of FASTQ that
+ * start at a header line and end after a quality line (less than 4 GiB; a chunk of at most 2 * max_bytes_per_batch
+ * bytes can never exceed the ctx's base limit).  The text is copied
+ * to the device, cut into records there (strict four-line records, LF or CRLF), packed into the slot's seq / qual /
+ * idx arrays and processed exactly as hpgq_batch_submit would process that batch.  The call returns after the
+ * parse (one stream synchronisation) and fills *info.  info->status != 0 means the chunk was NOT submitted (the
+ * slot stays free): HPGQ_TEXT_LINES (line count not a multiple of four, e.g. blank lines), HPGQ_TEXT_RECORD
+ * (record info->bad_record, counted from 0 in this chunk, has no '@' / '+' or sequence and quality differ in
+ * length), HPGQ_TEXT_TOO_MANY (more reads or bases than the ctx limits); the caller hands such a chunk to its
+ * host-side reader, which owns the diagnostics. */
+enum { HPGQ_TEXT_LINES = 1, HPGQ_TEXT_RECORD = 2, HPGQ_TEXT_TOO_MANY = 4 };
+typedef struct hpgq_text_info {
+  uint32_t n_reads, max_len;
+  uint64_t n_bases;
+  uint32_t n_lines;
+  uint32_t status;     /* 0 or HPGQ_TEXT_* bits */
+  uint32_t bad_record; /* first malformed record (HPGQ_TEXT_RECORD), else 0xFFFFFFFF */
+  uint32_t reserved;
+} hpgq_text_info_t;
+int hpgq_batch_submit_text(hpgq_ctx_t *ctx, const uint8_t *text, uint64_t n_bytes, int slot, hpgq_text_info_t *info);
+/* Header line of every read of the slot's text batch: byte offset inside `text` and length without the line
+ * terminator (n_reads entries each).  Valid between hpgq_batch_submit_text and the next submit on the slot. */
+int hpgq_batch_text_headers(hpgq_ctx_t *ctx, int slot, uint32_t *hdr_off, uint32_t *hdr_len);
 /* Blocks until the slot's work is finished and fills the result views. */
 int hpgq_batch_wait(hpgq_ctx_t *ctx, int slot, hpgq_batch_result_t *res);
 /* Same but copies nothing back (device-resident measurement); counters keep accumulating. */

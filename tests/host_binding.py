@@ -43,6 +43,8 @@ def lib():
         L.hq_reader_close.argtypes = [C.c_void_p]
         L.hq_reader_next.argtypes = [C.c_void_p, C.POINTER(HostBatch)]
         L.hq_reader_scan.argtypes = [C.c_void_p, C.POINTER(C.c_uint32), C.POINTER(C.c_uint64)]
+        L.hq_reader_peek_text.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+        L.hq_reader_advance.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64]
         L.hq_reader_error.restype = C.c_char_p
         L.hq_reader_error.argtypes = [C.c_void_p]
         L.hq_reader_data.restype = C.c_void_p
@@ -113,6 +115,19 @@ class Reader:
             n = b.n_reads
             tot = int(idx[n])
             yield seq[:tot].copy(), qual[:tot].copy(), idx[:n + 1].copy(), ho[:n].copy(), hl[:n].copy(), b.max_len
+
+    def text_chunks(self, max_bytes: int):
+        """Spans (off, len) of whole records as the device-parse path cuts them; stops at EOF, raises if no boundary."""
+        out = []
+        while True:
+            off, ln = C.c_uint64(0), C.c_uint64(0)
+            rc = lib().hq_reader_peek_text(self.h, C.c_uint64(max_bytes), C.byref(off), C.byref(ln))
+            if rc == 0:
+                return out
+            if rc < 0:
+                raise ValueError("no record boundary inside the budget")
+            out.append((off.value, ln.value))
+            lib().hq_reader_advance(self.h, ln, C.c_uint64(0))
 
     def close(self):
         if self.h:

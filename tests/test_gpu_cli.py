@@ -167,3 +167,48 @@ def test_multi_gpu_round_robin_same_files(q, ob, fastq):
     f2, _ = run_cli(fastq, "filter", FILTER_ARGS + ["--batch-size", "1500", "--gpus", "2"], "mg_f2")
     assert (f1 / "passed.fq").read_bytes() == (f2 / "passed.fq").read_bytes()
     assert (f1 / "failed.fq").read_bytes() == (f2 / "failed.fq").read_bytes()
+
+
+def _files(d):
+    # the .gnuplot scripts embed the output directory name
+    return {f: open(os.path.join(d, f), "rb").read() for f in sorted(os.listdir(d))
+            if f != "hpg-fastq.log" and not f.endswith(".gnuplot")}
+
+
+@pytest.mark.parametrize("command,args", [("stats", ["--kmers", "--batch-size", "4000"]),
+                                          ("filter", ["--read-length-range", "50,", "--max-N", "3", "--batch-size", "5000"]),
+                                          ("edit", ["--left-length", "8", "--left-quality-range", "25,", "--batch-size", "3000"])])
+def test_device_parser_and_host_reader_give_the_same_files(q, fastq, command, args):
+    """Default: records are cut on the GPU (hpgq_batch_submit_text); --host-parse: by hq_reader_next.  Same files."""
+    dev, _ = run_cli(fastq, command, args, f"devparse_{command}")
+    host, _ = run_cli(fastq, command, args + ["--host-parse"], f"hostparse_{command}")
+    log = open(dev / "hpg-fastq.log").read()
+    assert " 0 device-parsed" not in log and "device-parsed + 0 host-parsed" in log, log
+    assert "0 device-parsed" in open(host / "hpg-fastq.log").read()
+    a, b = _files(dev), _files(host)
+    assert a.keys() == b.keys() and len(a) > 0
+    for k in a:
+        assert a[k] == b[k], k
+
+
+def test_device_parser_hands_irregular_input_back(q, fastq, tmp_path):
+    """CRLF line ends are cut on the device; a blank line in the middle of the file sends the rest to the host reader."""
+    n = 6000
+    idx = fastq["idx"][:n + 1]
+    path = str(tmp_path / "crlf.fq")
+    data = hb.write_fastq(path, fastq["hdr"][:n], fastq["seq"], fastq["qual"], idx, eol=b"\r\n")
+    cut = data.index(b"@SYN.4100 ")
+    with open(path, "wb") as f:
+        f.write(data[:cut] + b"\r\n" + data[cut:] + b"\r\n\r\n")
+    outs = {}
+    for mode, extra in (("dev", []), ("host", ["--host-parse"])):
+        out = tmp_path / mode
+        out.mkdir()
+        r = subprocess.run([hb.CLI, "filter", "-f", path, "-o", str(out), "--read-quality-range", "20,", "--batch-size", "1500"]
+                           + extra, capture_output=True, text=True, cwd=str(out), timeout=600)
+        assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+        outs[mode] = _files(out)
+    log = open(tmp_path / "dev" / "hpg-fastq.log").read()
+    assert "handed the input back" in log and " 0 device-parsed" not in log
+    assert outs["dev"] == outs["host"]
+    assert outs["dev"]["passed.fq"].count(b"\n+\n") + outs["dev"]["failed.fq"].count(b"\n+\n") == n

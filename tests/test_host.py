@@ -133,6 +133,36 @@ def test_reader_rejects_malformed(tmp_path, text, what):
     r.close()
 
 
+@pytest.mark.parametrize("eol", [b"\n", b"\r\n"])
+def test_text_chunks_end_on_record_boundaries(q, tmp_path, eol):
+    """hq_reader_peek_text (device-parse path): every chunk is a run of whole records, also when quality lines start
+    with '@' or '+' (the boundary test is '@' now and '+' two lines on)."""
+    n = 3000
+    cfg = q.synth_cfg((20, 90), seed=77)
+    seq, qual, idx = q.synth_host(cfg, 0, n)
+    qual = qual.copy()
+    for i in range(n):  # hostile quality lines: '@' / '+' as first byte of every other read
+        if idx[i + 1] > idx[i] and i % 2 == 0:
+            qual[idx[i]] = ord("@") if i % 4 == 0 else ord("+")
+    hdr = [b"@r%d +x @y" % i for i in range(n)]
+    path = str(tmp_path / "c.fq")
+    data = hb.write_fastq(path, hdr, seq, qual, idx, eol=eol)
+    starts = set()
+    pos = 0
+    for i in range(n):
+        starts.add(pos)
+        pos += len(hdr[i]) + 2 * int(idx[i + 1] - idx[i]) + 1 + 4 * len(eol)
+    assert pos == len(data)
+    for budget in (700, 4096, 50000, len(data), 2 * len(data)):
+        r = hb.Reader(path)
+        chunks = r.text_chunks(budget)
+        r.close()
+        assert chunks[0][0] == 0 and sum(c[1] for c in chunks) == len(data)
+        for off, ln in chunks:
+            assert off in starts and 0 < ln <= max(budget, 1)
+            assert off + ln == len(data) or (off + ln) in starts
+
+
 def test_writer_matches_record_layout(q, tmp_path):
     """header, sequence, '+', quality, each newline-terminated, in the order given by src."""
     seq, qual, idx = synth_reads(q, 300, seed=11)
