@@ -1,6 +1,7 @@
 // hpgq_api.cu -- implementation of the C ABI in include/hpg_fastq_cuda.h.
 // One ctx per GPU, used by one host thread; n_slots streams double-buffer H2D copies against
 // kernels; the flat u64 counter block lives on the device for the whole run.
+#include <thread>
 #include <cuda_runtime.h>
 #include <stdio.h>
 #include <stdlib.h>

@@ -69,8 +69,13 @@ uint64_t hq_reader_size(const hq_reader_t *r) { return r->size; }
 const char *hq_reader_error(const hq_reader_t *r) { return r->err; }
 
 int hq_reader_scan(hq_reader_t *r, uint32_t *max_line, uint64_t *n_lines) {
+  return hq_reader_scan_prefix(r, r->size, max_line, n_lines);
+}
+
+int hq_reader_scan_prefix(hq_reader_t *r, uint64_t limit, uint32_t *max_line, uint64_t *n_lines) {
   uint64_t p = 0, lines = 0, mx = 0;
-  while (p < r->size) {
+  if (limit > r->size) limit = r->size;
+  while (p < limit) {
     const uint8_t *nl = (const uint8_t *)memchr(r->data + p, '\n', r->size - p);
     uint64_t e = nl ? (uint64_t)(nl - r->data) : r->size;
     uint64_t len = e - p;

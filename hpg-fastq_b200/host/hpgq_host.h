@@ -91,6 +91,9 @@ const uint8_t *hq_reader_data(const hq_reader_t *r); /* the mapped input (header
 uint64_t hq_reader_size(const hq_reader_t *r);
 /* longest line of the file and number of lines, one memchr pass (sizes Lcap before the first batch) */
 int hq_reader_scan(hq_reader_t *r, uint32_t *max_line, uint64_t *n_lines);
+/* same over the lines that start in the first `limit` bytes (filter / edit keep no per-position tables: a sample
+ * is enough to size their batches) */
+int hq_reader_scan_prefix(hq_reader_t *r, uint64_t limit, uint32_t *max_line, uint64_t *n_lines);
 /* Fills b with up to b->cap_reads records / b->cap_bytes bases.  Returns 1 if reads were produced, 0 at EOF,
  * < 0 on a malformed record (message in hq_reader_error). */
 int hq_reader_next(hq_reader_t *r, hq_host_batch_t *b);

@@ -71,17 +71,24 @@ typedef struct run {
   uint64_t n_text_batches, n_host_batches;
 } run_t;
 
-static int alloc_host_batch(hq_host_batch_t *b, uint32_t cap_reads, uint64_t cap_bytes) {
+/* the pinned SoA arrays are only needed by the host reader: with the device parser they are allocated when (if)
+ * the input is handed back (pinning hundreds of MB costs more than parsing them) */
+static int alloc_host_soa(hq_host_batch_t *b) {
+  int rc;
+  if (b->seq) return 0;
+  if ((rc = hpgq_host_alloc_pinned(b->cap_bytes + 64, (void **)&b->seq))) return rc;
+  if ((rc = hpgq_host_alloc_pinned(b->cap_bytes + 64, (void **)&b->qual))) return rc;
+  return hpgq_host_alloc_pinned(((size_t)b->cap_reads + 1) * 4 + 64, (void **)&b->idx);
+}
+
+static int alloc_host_batch(hq_host_batch_t *b, uint32_t cap_reads, uint64_t cap_bytes, int with_soa) {
   memset(b, 0, sizeof *b);
   b->cap_reads = cap_reads;
   b->cap_bytes = cap_bytes;
-  int rc;
-  if ((rc = hpgq_host_alloc_pinned(cap_bytes + 64, (void **)&b->seq))) return rc;
-  if ((rc = hpgq_host_alloc_pinned(cap_bytes + 64, (void **)&b->qual))) return rc;
-  if ((rc = hpgq_host_alloc_pinned(((size_t)cap_reads + 1) * 4 + 64, (void **)&b->idx))) return rc;
   b->hdr_off = (uint64_t *)malloc((size_t)cap_reads * sizeof(uint64_t));
   b->hdr_len = (uint32_t *)malloc((size_t)cap_reads * sizeof(uint32_t));
-  return (b->hdr_off && b->hdr_len) ? 0 : HPGQ_ERR_NOMEM;
+  if (!b->hdr_off || !b->hdr_len) return HPGQ_ERR_NOMEM;
+  return with_soa ? alloc_host_soa(b) : 0;
 }
 
 static void free_host_batch(hq_host_batch_t *b) {
@@ -163,6 +170,8 @@ static int run_pipeline(run_t *r) {
       r->device_parse = 0;
       logf_("INFO", "device FASTQ parser handed the input back to the host reader");
     }
+    int arc = alloc_host_soa(hb);
+    if (arc) return die_hpgq("pinned batch allocation", arc);
     int got = hq_reader_next(r->reader, hb);
     if (got < 0) {
       fprintf(stderr, "\nFATAL: %s: %s\n", r->o->in_filename, hq_reader_error(r->reader));
@@ -210,7 +219,10 @@ static int run_command(hq_options_t *o) {
   uint32_t max_line = (uint32_t)o->max_read_len;
   if (max_line == 0) {
     uint64_t n_lines = 0;
-    if (hq_reader_scan(r->reader, &max_line, &n_lines)) {
+    /* stats sizes the per-position tables from the longest read of the whole file; filter / edit only size their
+     * batches (cut by bytes anyway), so the first 64 MB are sample enough */
+    const uint64_t scan_bytes = o->command == HQ_CMD_STATS ? hq_reader_size(r->reader) : (64ull << 20);
+    if (hq_reader_scan_prefix(r->reader, scan_bytes, &max_line, &n_lines)) {
       fprintf(stderr, "\nFATAL: %s holds a line longer than 4 GiB\n", o->in_filename);
       goto out;
     }
@@ -254,7 +266,7 @@ static int run_command(hq_options_t *o) {
       goto out;
     }
     for (int s = 0; s < HQ_SLOTS; s++)
-      if ((rc = alloc_host_batch(&r->hb[g][s], lim.max_reads_per_batch, cap_bytes))) {
+      if ((rc = alloc_host_batch(&r->hb[g][s], lim.max_reads_per_batch, cap_bytes, o->host_parse))) {
         die_hpgq("pinned batch allocation", rc);
         goto out;
       }
@@ -279,7 +291,9 @@ static int run_command(hq_options_t *o) {
     goto out;
   }
 
+  const double t1 = now_s();
   if (run_pipeline(r)) goto out;
+  const double t2 = now_s();
 
   if (r->w_pass && hq_writer_close(r->w_pass)) {
     r->w_pass = NULL;
@@ -358,6 +372,8 @@ static int run_command(hq_options_t *o) {
     snprintf(msg, sizeof msg, "%s: %lu reads on %d GPU(s) in %.3f s (%.3g reads/s, %lu device-parsed + %lu host-parsed batches, %s)",
              o->command_name, (unsigned long)r->num_reads, r->n_gpus, dt, dt > 0 ? (double)r->num_reads / dt : 0.0,
              (unsigned long)r->n_text_batches, (unsigned long)r->n_host_batches, hpgq_version());
+    logf_("INFO", msg);
+    snprintf(msg, sizeof msg, "phases: setup %.3f s, batches %.3f s, merge + report %.3f s", t1 - t0, t2 - t1, now_s() - t2);
     logf_("INFO", msg);
   }
   status = 0;
