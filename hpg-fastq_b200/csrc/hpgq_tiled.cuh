@@ -6,7 +6,7 @@
 //
 // Shape (DESIGN.md "stats+filter kernel"):
 //   * persistent grid, one CTA per SM; one producer thread streams tiles of RT consecutive reads (seq
-//     bytes, qual bytes, offsets) into a 3-stage shared-memory ring with 1-D bulk async copies (TMA
+//     bytes, qual bytes, offsets) into a 2-stage shared-memory ring with 1-D bulk async copies (TMA
 //     engine, cp.async.bulk + mbarrier complete_tx): HBM is read exactly once, nothing is re-read;
 //   * 15 consumer warps; a group of G lanes owns one read per iteration, lane `lig` owns the K words
 //     {lig + k*G} (4 positions each) of the read frame.  K and G are template parameters, so all
