@@ -62,6 +62,8 @@ struct hpgq_slot {
   hq_parse_bufs pb = {};
   uint32_t *h_pinfo = nullptr;  // pinned copy of pb.info
   bool text_batch = false;
+  uint8_t *d_otext = nullptr, *h_otext = nullptr;  // FASTQ text of the compacted output (hpgq_batch_wait_text)
+  uint64_t otext_cap = 0;
 };
 
 struct hpgq_ctx {
@@ -180,6 +182,7 @@ static void slot_free(hpgq_slot &s) {
   cudaFreeHost(s.h_out_seq); cudaFreeHost(s.h_out_qual); cudaFreeHost(s.h_out_idx); cudaFreeHost(s.h_out_src);
   cudaFreeHost(s.h_lens);
   cudaFree(s.d_text); cudaFreeHost(s.h_text); cudaFreeHost(s.h_pinfo);
+  cudaFree(s.d_otext); cudaFreeHost(s.h_otext);
   cudaFree(s.pb.tile_cnt); cudaFree(s.pb.cta_sum); cudaFree(s.pb.nl); cudaFree(s.pb.info);
   cudaFree(s.pb.seq_off); cudaFree(s.pb.qual_off); cudaFree(s.pb.hdr_off); cudaFree(s.pb.hdr_len);
   if (s.ev0) cudaEventDestroy(s.ev0);

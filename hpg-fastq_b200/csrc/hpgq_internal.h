@@ -90,3 +90,7 @@ struct hq_parse_bufs {
   uint32_t *idx;
 };
 cudaError_t hq_launch_parse(const hq_parse_bufs &b, int sm_count, cudaStream_t st, uint64_t *launches);
+// FASTQ text of a text batch's compacted output (passed records, then failed); rec: n + 1 words of scratch,
+// oinfo: [0] = bytes of the passed records, [1] = bytes of all records
+cudaError_t hq_launch_compose(const hq_parse_bufs &b, uint32_t n, const hq_compact_bufs &cb, uint32_t *rec, uint32_t *oinfo,
+                              uint8_t *otext, int sm_count, cudaStream_t st, uint64_t *launches);

@@ -252,7 +252,88 @@ __global__ void __launch_bounds__(PT) hq_parse_gather(const uint8_t *text, const
   }
 }
 
+// ------------------------------------------------------------------ FASTQ text of the compacted output
+// Output read k (passed reads first, then failed, each in input order: hq_compact_*) becomes the record
+//   header of source read out_src[k] '\n' sequence '\n' '+' '\n' quality '\n'
+// (the reference's fastq_fwrite layout).  rec[k+1] first holds the record length, then (in place)
+// the end offset; oinfo[0] = bytes of the passed records, oinfo[1] = bytes of all records.
+__global__ void __launch_bounds__(PT) hq_compose_len(uint32_t n, const uint32_t *out_idx, const uint32_t *out_src,
+                                                   const uint32_t *hdr_len, uint32_t *rec, uint32_t *cta_sum) {
+  __shared__ uint32_t ws[PT / 32];
+  uint32_t rb, re;
+  hq_parse_range(n, &rb, &re);
+  uint32_t sum = 0;
+  for (uint32_t k = rb + threadIdx.x; k < re; k += PT) {
+    const uint32_t len = hdr_len[out_src[k]] + 2u * (out_idx[k + 1u] - out_idx[k]) + 5u;
+    rec[k + 1u] = len;
+    sum += len;
+  }
+  uint32_t tot;
+  (void)block_excl_scan(sum, ws, &tot);
+  if (threadIdx.x == 0) cta_sum[blockIdx.x] = tot;
+}
+
+__global__ void __launch_bounds__(PT) hq_compose_off(uint32_t n, uint32_t *rec, const uint32_t *cta_off) {
+  __shared__ uint32_t ws[PT / 32];
+  if (blockIdx.x == 0 && threadIdx.x == 0) rec[0] = 0u;
+  uint32_t rb, re;
+  hq_parse_range(n, &rb, &re);
+  uint32_t run = cta_off[blockIdx.x];
+  for (uint32_t k0 = rb; k0 < re; k0 += PT) {
+    const uint32_t k = k0 + threadIdx.x;
+    const uint32_t len = k < re ? rec[k + 1u] : 0u;
+    uint32_t tot;
+    const uint32_t ex = block_excl_scan(len, ws, &tot);
+    if (k < re) rec[k + 1u] = run + ex + len;
+    run += tot;
+  }
+}
+
+__global__ void __launch_bounds__(PT) hq_compose_gather(uint32_t n, const uint8_t *text, const uint32_t *hdr_off,
+                                                      const uint32_t *hdr_len, const uint8_t *out_seq, const uint8_t *out_qual,
+                                                      const uint32_t *out_idx, const uint32_t *out_src, const uint32_t *rec,
+                                                      const uint32_t *totals, uint32_t *oinfo, uint8_t *otext) {
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    oinfo[0] = rec[min(totals[0], n)];
+    oinfo[1] = rec[n];
+  }
+  const uint32_t lane = threadIdx.x & 31u;
+  const uint32_t warps = gridDim.x * (PT / 32);
+  for (uint32_t k = blockIdx.x * (PT / 32) + (threadIdx.x >> 5); k < n; k += warps) {
+    const uint32_t src = out_src[k], o = out_idx[k], L = out_idx[k + 1u] - o, H = hdr_len[src];
+    uint8_t *d = otext + rec[k];
+    const uint8_t *h = text + hdr_off[src];
+    for (uint32_t j = lane; j < H; j += 32u) d[j] = h[j];
+    d += H;
+    const uint8_t *sq = out_seq + o, *ql = out_qual + o;
+    for (uint32_t j = lane; j < L; j += 32u) {
+      d[1u + j] = sq[j];
+      d[L + 4u + j] = ql[j];
+    }
+    if (lane == 0) {
+      d[0] = '\n';
+      d[L + 1u] = '\n';
+      d[L + 2u] = '+';
+      d[L + 3u] = '\n';
+      d[2u * L + 4u] = '\n';
+    }
+  }
+}
+
 }  // namespace
+
+cudaError_t hq_launch_compose(const hq_parse_bufs &b, uint32_t n, const hq_compact_bufs &cb, uint32_t *rec, uint32_t *oinfo,
+                              uint8_t *otext, int sm_count, cudaStream_t st, uint64_t *launches) {
+  if (!n) return cudaMemsetAsync(oinfo, 0, 8, st);
+  const int grid = sm_count * 8;
+  hq_compose_len<<<grid, PT, 0, st>>>(n, cb.out_idx, cb.out_src, b.hdr_len, rec, b.cta_sum);
+  hq_parse_scan<<<1, 1024, 0, st>>>(b.cta_sum, (uint32_t)grid, oinfo + 1, nullptr, 0, nullptr, 0);
+  hq_compose_off<<<grid, PT, 0, st>>>(n, rec, b.cta_sum);
+  hq_compose_gather<<<grid, PT, 0, st>>>(n, b.text, b.hdr_off, b.hdr_len, cb.out_seq, cb.out_qual, cb.out_idx, cb.out_src, rec,
+                                        cb.totals, oinfo, otext);
+  *launches += 4;
+  return cudaGetLastError();
+}
 
 cudaError_t hq_launch_parse(const hq_parse_bufs &b, int sm_count, cudaStream_t st, uint64_t *launches) {
   const uint32_t n = b.n_bytes;

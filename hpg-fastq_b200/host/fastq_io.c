@@ -274,6 +274,12 @@ int hq_writer_put(hq_writer_t *w, const uint8_t *file_data, const hq_host_batch_
   return w->failed ? -1 : 0;
 }
 
+int hq_writer_put_raw(hq_writer_t *w, const uint8_t *text, uint64_t n) {
+  /* large blocks go to write() directly (after the buffered bytes), without another copy */
+  wput(w, text, (size_t)n);
+  return w->failed ? -1 : 0;
+}
+
 int hq_writer_close(hq_writer_t *w) {
   if (!w) return 0;
   wflush(w);

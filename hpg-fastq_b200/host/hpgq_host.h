@@ -116,6 +116,9 @@ int hq_writer_close(hq_writer_t *w); /* 0 ok, < 0 if any write failed */
 int hq_writer_put(hq_writer_t *w, const uint8_t *file_data, const hq_host_batch_t *b, const uint8_t *seq,
                   const uint8_t *qual, const uint32_t *idx, const uint32_t *src, uint32_t from, uint32_t to);
 
+/* finished FASTQ text (records composed on the device, hpgq_batch_wait_text) */
+int hq_writer_put_raw(hq_writer_t *w, const uint8_t *text, uint64_t n);
+
 /* ------------------------------------------------------------------ report */
 typedef struct hq_kmer {
   int id;

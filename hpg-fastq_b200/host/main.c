@@ -63,11 +63,11 @@ typedef struct run {
   hpgq_ctx_t *ctx[HQ_MAX_GPUS];
   hq_host_batch_t hb[HQ_MAX_GPUS][HQ_SLOTS];
   int busy[HQ_MAX_GPUS][HQ_SLOTS];
+  int is_text[HQ_MAX_GPUS][HQ_SLOTS]; /* the slot's batch went through the device parser */
   hq_writer_t *w_pass, *w_fail;
   uint64_t num_passed, num_failed, num_edited, num_reads;
   int device_parse;      /* records are cut on the GPU until a chunk is handed back */
   uint64_t text_budget;  /* bytes of FASTQ text per device-parsed batch */
-  uint32_t *tmp_off;     /* batch_size header offsets inside a chunk */
   uint64_t n_text_batches, n_host_batches;
 } run_t;
 
@@ -103,10 +103,30 @@ static void free_host_batch(hq_host_batch_t *b) {
 /* consumer stage for one retired slot */
 static int consume(run_t *r, int g, int s) {
   hpgq_batch_result_t res;
-  int rc = hpgq_batch_wait(r->ctx[g], s, &res);
+  const hq_options_t *o = r->o;
+  int rc;
+  if (r->is_text[g][s] && o->command != HQ_CMD_STATS) {
+    /* device-parsed batch: the output records were composed on the GPU, the consumer only writes them */
+    const uint8_t *text = NULL;
+    uint64_t pbytes = 0, fbytes = 0;
+    if ((rc = hpgq_batch_wait_text(r->ctx[g], s, &res, &text, &pbytes, &fbytes))) return die_hpgq("hpgq_batch_wait_text", rc);
+    r->busy[g][s] = 0;
+    r->num_reads += res.n_reads;
+    r->num_edited += res.n_edited;
+    const int filtering_t = o->command == HQ_CMD_FILTER || o->filter_on;
+    if (filtering_t) {
+      r->num_passed += res.n_passed;
+      r->num_failed += res.n_failed;
+    }
+    if (hq_writer_put_raw(r->w_pass, text, pbytes) || (fbytes && (!r->w_fail || hq_writer_put_raw(r->w_fail, text + pbytes, fbytes)))) {
+      fprintf(stderr, "\nFATAL: write error on the output FASTQ files\n");
+      return 1;
+    }
+    return 0;
+  }
+  rc = hpgq_batch_wait(r->ctx[g], s, &res);
   if (rc) return die_hpgq("hpgq_batch_wait", rc);
   r->busy[g][s] = 0;
-  const hq_options_t *o = r->o;
   const hq_host_batch_t *b = &r->hb[g][s];
   const uint8_t *fd = hq_reader_data(r->reader);
   r->num_reads += res.n_reads;
@@ -151,12 +171,9 @@ static int run_pipeline(run_t *r) {
         if (info.status == 0) {
           hb->n_reads = info.n_reads;
           hb->max_len = info.max_len;
-          if (r->o->command != HQ_CMD_STATS) { /* the writer needs the header lines */
-            if ((rc = hpgq_batch_text_headers(r->ctx[g], s, r->tmp_off, hb->hdr_len))) return die_hpgq("hpgq_batch_text_headers", rc);
-            for (uint32_t i = 0; i < info.n_reads; i++) hb->hdr_off[i] = off + r->tmp_off[i];
-          }
           hq_reader_advance(r->reader, len, info.n_reads);
           r->busy[g][s] = 1;
+          r->is_text[g][s] = 1;
           r->n_text_batches++;
           continue;
         }
@@ -183,6 +200,7 @@ static int run_pipeline(run_t *r) {
     int rc = hpgq_batch_submit(r->ctx[g], &hbatch, s);
     if (rc) return die_hpgq("hpgq_batch_submit", rc);
     r->busy[g][s] = 1;
+    r->is_text[g][s] = 0;
     r->n_host_batches++;
   }
   /* drain in batch order: the oldest outstanding batch is b - N*HQ_SLOTS */
@@ -273,8 +291,6 @@ static int run_command(hq_options_t *o) {
   }
   r->device_parse = !o->host_parse;
   r->text_budget = 2 * cap_bytes; /* bases are less than half of the text, so a chunk never exceeds cap_bytes bases */
-  r->tmp_off = (uint32_t *)malloc(((size_t)lim.max_reads_per_batch + 1) * sizeof(uint32_t));
-  if (!r->tmp_off) goto out;
   if (o->command == HQ_CMD_FILTER) {
     snprintf(pass_name, sizeof pass_name, "%s/passed.fq", o->out_dirname); /* src/filter_fastq.c:185 */
     snprintf(fail_name, sizeof fail_name, "%s/failed.fq", o->out_dirname); /* src/filter_fastq.c:189 */
@@ -385,7 +401,6 @@ out:
     for (int s = 0; s < HQ_SLOTS; s++) free_host_batch(&r->hb[g][s]);
   }
   if (r->reader) hq_reader_close(r->reader);
-  free(r->tmp_off);
   free(r);
   return status;
 }

@@ -102,7 +102,7 @@ DEFAULT_SEED = 0x48504751
 EXPORTS = [
     "hpgq_strerror", "hpgq_last_error", "hpgq_layout", "hpgq_device_count", "hpgq_ctx_create", "hpgq_ctx_destroy",
     "hpgq_set_params", "hpgq_get_layout", "hpgq_batch_submit", "hpgq_batch_submit_device", "hpgq_batch_wait",
-    "hpgq_batch_submit_text", "hpgq_batch_text_headers",
+    "hpgq_batch_submit_text", "hpgq_batch_text_headers", "hpgq_batch_wait_text",
     "hpgq_batch_sync", "hpgq_batch_device_views", "hpgq_counters_reset", "hpgq_counters_download",
     "hpgq_counters_device_ptr", "hpgq_counters_reduce", "hpgq_counters_finalize_host", "hpgq_slot_stream", "hpgq_launch_count",
     "hpgq_last_kernel_ms", "hpgq_synth_device", "hpgq_synth_host", "hpgq_dev_alloc", "hpgq_dev_free",
@@ -257,6 +257,18 @@ class Ctx:
         _ck(self.lib.hpgq_batch_text_headers(self.h, C.c_int(slot), C.c_void_p(off.ctypes.data), C.c_void_p(ln.ctypes.data)),
             "hpgq_batch_text_headers")
         return off[:n_reads], ln[:n_reads]
+
+    def wait_text(self, slot: int = 0) -> dict:
+        """hpgq_batch_wait_text: counts + the output FASTQ text (passed records, failed records) as bytes."""
+        r = Result()
+        text = C.c_void_p()
+        pb, fb = C.c_uint64(0), C.c_uint64(0)
+        _ck(self.lib.hpgq_batch_wait_text(self.h, C.c_int(slot), C.byref(r), C.byref(text), C.byref(pb), C.byref(fb)),
+            "hpgq_batch_wait_text")
+        tot = pb.value + fb.value
+        raw = C.string_at(text.value, tot) if tot else b""
+        return dict(n_reads=r.n_reads, n_passed=r.n_passed, n_failed=r.n_failed, n_edited=r.n_edited,
+                    passed_text=raw[:pb.value], failed_text=raw[pb.value:])
 
     def wait(self, slot: int = 0) -> dict:
         r = Result()

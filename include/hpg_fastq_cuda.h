@@ -222,6 +222,14 @@ int hpgq_batch_submit_text(hpgq_ctx_t *ctx, const uint8_t *text, uint64_t n_byte
 /* Header line of every read of the slot's text batch: byte offset inside `text` and length without the line
  * terminator (n_reads entries each).  Valid between hpgq_batch_submit_text and the next submit on the slot. */
 int hpgq_batch_text_headers(hpgq_ctx_t *ctx, int slot, uint32_t *hdr_off, uint32_t *hdr_len);
+/* hpgq_batch_wait for a text batch submitted with HPGQ_WORK_COMPACT: instead of the compacted seq / qual / idx / src
+ * arrays the device writes the output FASTQ records themselves (header of the source read, sequence, "+", quality,
+ * each '\n'-terminated: the layout of fastq_fwrite(), reference call sites src/filter_fastq.c:165-169,
+ * src/edit_fastq.c:190-198) and only that text comes back: *text (pinned, valid until the slot is reused) holds the
+ * passed reads' records in input order in its first *passed_bytes bytes, then *failed_bytes bytes of failed reads'
+ * records.  res gets the counts (n_reads, n_passed, n_failed, n_edited) and no array views. */
+int hpgq_batch_wait_text(hpgq_ctx_t *ctx, int slot, hpgq_batch_result_t *res, const uint8_t **text,
+                         uint64_t *passed_bytes, uint64_t *failed_bytes);
 /* Blocks until the slot's work is finished and fills the result views. */
 int hpgq_batch_wait(hpgq_ctx_t *ctx, int slot, hpgq_batch_result_t *res);
 /* Same but copies nothing back (device-resident measurement); counters keep accumulating. */

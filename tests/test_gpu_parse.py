@@ -166,3 +166,37 @@ def test_bytes_that_look_like_line_breaks(q, ob):
     assert np.array_equal(goff, hoff) and np.array_equal(glen, hlen)
     exp, _, _ = ob.process_batch(par, lay, seq, qual, idx)
     assert not diff_counters(q, got, exp)
+
+
+@pytest.mark.parametrize("eol", [b"\n", b"\r\n"])
+@pytest.mark.parametrize("work_filter", [True, False])
+def test_output_records_composed_on_the_device(q, ob, eol, work_filter):
+    """hpgq_batch_wait_text: passed.fq / failed.fq (edit.fq) bytes straight from the device = the writer's layout
+    (header of the source read, sequence, '+', quality, LF-terminated) over the oracle's compacted batch."""
+    n = 12345
+    cfg = q.synth_cfg((20, 150), short_pct=2)
+    seq, qual, idx = q.synth_host(cfg, 3, n)
+    hdr = lambda i: b"@r%d %s" % (i, b"x" * (i % 23))
+    text, _, _ = make_text(seq, qual, idx, eol=eol, hdr=hdr)
+    work = q.WORK_EDIT | q.WORK_COMPACT | (q.WORK_FILTER if work_filter else 0)
+    par = q.make_params(work, filter=FILTER if work_filter else None,
+                        edit=dict(left_length=10, min_left_quality=20, right_length=10, min_right_quality=20))
+    with q.Ctx(0, max_reads=n, max_bytes=int(idx[-1]) + 64, max_read_len=192) as ctx:
+        ctx.set_params(par)
+        info = ctx.submit_text(text, 0)
+        assert info.status == 0
+        res = ctx.wait_text(0)
+        lay = ctx.layout
+    _, emask, etrim = ob.process_batch(par, lay, seq, qual, idx)
+    exp = ob.compact(seq, qual, idx, emask if work_filter else None, etrim)
+    oseq, oqual, oidx, osrc = exp["out_seq"].tobytes(), exp["out_qual"].tobytes(), exp["out_idx"], exp["out_src"]
+
+    def records(a, b):
+        return b"".join(hdr(int(osrc[k])) + b"\n" + oseq[oidx[k]:oidx[k + 1]] + b"\n+\n" + oqual[oidx[k]:oidx[k + 1]] + b"\n"
+                        for k in range(a, b))
+
+    npass = exp["n_passed"] if work_filter else n
+    assert res["n_passed"] == npass and res["n_reads"] == n
+    assert res["passed_text"] == records(0, npass)
+    assert res["failed_text"] == records(npass, n)
+    assert res["n_edited"] == int((etrim[:, 1] != np.diff(idx.astype(np.int64))).sum())
