@@ -52,6 +52,7 @@ typedef struct hq_options {
   int k2;              /* --kmers2 K: second k-mer size (BASELINE.json: 11), stats only             */
   int cg_k;            /* --chaos-game K: chaos-game word size (old/chaos_game.c), stats only       */
   int host_parse;      /* --host-parse: records are cut by hq_reader_next, not by the device parser */
+  char *cg_signature;  /* --chaos-game-signature FILE: reference genomic signature for the difference image */
 } hq_options_t;
 
 /* Parses argv (argv[0] = command name, as in src/hpg-fastq.c:55-57).  Returns NULL after printing the
@@ -136,6 +137,30 @@ void hq_kmers_sorted(const hpgq_layout_t *lay, const uint64_t *block, hq_kmer_t 
 /* stats_report() (src/stats_report.c:32-56): writes <outdir>/<basename(in)>.summary.txt and the data /
  * gnuplot files from a finalized counter block.  Returns 0 or -1 (errno set). */
 int hq_stats_report(const hpgq_layout_t *lay, const uint64_t *block, const hq_options_t *opts);
+
+/* ------------------------------------------------------------------ chaos-game post-processing (chaos_post.c) */
+typedef struct hq_cg_diff_stats {
+  int highest, lowest; /* chaos_game_data_t.highest_table_dif_value / lowest_table_dif_value */
+  double mean, sd;     /* mean_table_dif_value / standard_deviation_table_dif_value          */
+  double fq_norm, gs_norm;
+} hq_cg_diff_stats_t;
+
+/* flat row-major dim x dim tables (dim = 2^k), u64 cells as in the counter block; pix = dim * dim grey values */
+void hq_cg_pixels_seq(const uint64_t *table_seq, uint32_t dim, uint64_t fq_word_count, uint8_t *pix);
+void hq_cg_pixels_quality(const uint64_t *table_seq, const uint64_t *table_q, uint32_t dim, int k, uint8_t *pix);
+void hq_cg_pixels_diff(const int32_t *dif, uint32_t dim, uint8_t *pix);
+/* genomic-signature file: 196-byte header_gs_t, then dim rows of dim 32-bit cells (old/chaos_game.c:298-320) */
+int hq_cg_load_signature(const char *path, uint32_t dim, uint32_t *table_gs, uint32_t *ref_word_count);
+/* normalised difference matrix + its range, mean and standard deviation (old/chaos_game.c:322-405); -1 if a
+ * word count is 0 (the reference aborts there) */
+int hq_cg_diff(const uint64_t *table_seq, const uint32_t *table_gs, uint32_t dim, uint64_t fq_word_count,
+               uint32_t ref_word_count, int32_t *dif, hq_cg_diff_stats_t *st);
+/* binary PGM; k < 7 is zoomed to 128 x 128 (old/chaos_game.c:514-593) */
+int hq_cg_write_pgm(const char *path, const uint8_t *pix, uint32_t dim, int k);
+/* <out_dir>/<basename(fq_path)>_k=<k>_FG.pgm, _QQ.pgm and, with a signature file, _FG_dif.pgm
+ * (old/chaos_game.c:407-465).  0 ok, -1 I/O error, -2 no words counted, -3 bad signature file */
+int hq_cg_write_images(const hpgq_layout_t *lay, const uint64_t *block, const char *fq_path, const char *out_dir,
+                       const char *signature_path, hq_cg_diff_stats_t *st_out);
 
 #ifdef __cplusplus
 }

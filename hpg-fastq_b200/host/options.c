@@ -48,6 +48,7 @@ static const hq_optdef_t OPTS[] = {
     {NULL, "kmers2", A_INT, "[B200] also count k-mers of this size (eg. 11)", C_S, 1},
     {NULL, "chaos-game", A_INT, "[B200] chaos-game frequency matrices of this word size (eg. 10)", C_S, 1},
     {NULL, "host-parse", A_LIT, "[B200] cut the FastQ records on the host instead of on the GPU", C_ALL, 1},
+    {NULL, "chaos-game-signature", A_STR, "[B200] genomic signature file (.gs) for the chaos-game difference image", C_S, 1},
 };
 #define N_OPTS ((int)(sizeof OPTS / sizeof OPTS[0]))
 
@@ -103,6 +104,7 @@ void hq_options_free(hq_options_t *o) {
   free(o->read_quality_range);
   free(o->left_quality_range);
   free(o->right_quality_range);
+  free(o->cg_signature);
   free(o->in_filename);
   free(o->out_dirname);
   free(o->exec_name);
@@ -143,6 +145,7 @@ static int set_option(hq_options_t *o, int i, const char *val) {
     case 17: o->k2 = iv; break;
     case 18: o->cg_k = iv; break;
     case 19: o->host_parse = 1; break;
+    case 20: SETS(cg_signature); break;
     default: return 0;
   }
 #undef SETS

@@ -358,6 +358,22 @@ static int report_extensions(const ctx_t *c) {
       }
       if (fclose(f)) return -1;
     }
+    /* the reference's own chaos-game outputs: the PGM images (old/chaos_game.c:407-465) and, with a signature
+     * file, the figures of the difference matrix (:322-405) */
+    hq_cg_diff_stats_t st;
+    const int rc = hq_cg_write_images(lay, c->blk, c->o->in_filename, c->o->out_dirname, c->o->cg_signature, &st);
+    if (rc == -1 || rc == -3) return -1;
+    if (rc == 0 && c->o->cg_signature) {
+      char suffix[64];
+      snprintf(suffix, sizeof suffix, "chaos.k%u.diff.txt", lay->cg_k);
+      FILE *f = open_out(c, suffix, data, sizeof data);
+      if (!f) return -1;
+      fprintf(f, "Fastq file normalization ratio = %12.6f\n", st.fq_norm);       /* old/chaos_game.c:339 */
+      fprintf(f, "Genomic signature normalization ratio = %12.6f\n", st.gs_norm); /* :351 */
+      fprintf(f, "Interval of variation of diff matrix values = [%d, %d]\n", st.highest, st.lowest); /* :375 */
+      fprintf(f, "Mean of diff matrix values = %f\nStandard deviation of diff matrix values = %f\n", st.mean, st.sd);
+      if (fclose(f)) return -1;
+    }
   }
   return 0;
 }

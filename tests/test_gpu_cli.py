@@ -110,6 +110,47 @@ def test_stats_extensions_k11_and_chaos(q, ob, fastq):
     assert np.array_equal(qual.reshape(-1), lay.section(blk, "CG_Q")[:128 * 128])
 
 
+@pytest.mark.parametrize("k", [6, 8])
+def test_chaos_game_images_equal_the_reference_code(q, ob, fastq, k):
+    """--chaos-game K --chaos-game-signature F: the three PGM files are the ones the reference's own
+    chaos_game_write_table_images (old/chaos_game.c:407-465, oracle/_ref) writes from the same tables."""
+    import shutil
+    import struct
+    import tempfile
+    ref = ob.ref_lib()
+    if ref is None:
+        pytest.skip("oracle/_ref was not built")
+    dim = 1 << k
+    work = tempfile.mkdtemp(prefix="cg", dir="/tmp")  # short paths: the reference formats names into 100-byte buffers
+    try:
+        rng = np.random.default_rng(k)
+        gs = rng.integers(0, 40, size=(dim, dim), dtype=np.uint32)
+        gs_path = os.path.join(work, "ref.gs")
+        with open(gs_path, "wb") as f:
+            f.write(b"ref.gs".ljust(180, b"\0") + struct.pack("<4I", k, dim, dim, int(gs.sum())))
+            f.write(gs.astype("<u4").tobytes())
+        args = ["--chaos-game", str(k), "--chaos-game-signature", gs_path]
+        out, _ = run_cli(fastq, "stats", args, f"stats_cgimg{k}")
+        par, lay, blk, _, _ = oracle_for(q, ob, fastq, "stats", args)
+        seq = lay.section(blk, "CG_SEQ")[:dim * dim].astype(np.uint32)
+        tq = lay.section(blk, "CG_Q")[:dim * dim].astype(np.uint32)
+        rdif = np.zeros(dim * dim, dtype=np.int32)
+        hi, lo, rw = C.c_int(0), C.c_int(0), C.c_uint(0)
+        refdir = os.path.join(work, "r")
+        os.mkdir(refdir)
+        p = lambda a: a.ctypes.data_as(C.c_void_p)
+        assert ref.ref_chaos_post(C.c_int(k), p(seq), p(tq), C.c_uint(int(blk[q.S["CG_WORDS"]])), gs_path.encode(),
+                                  fastq["path"].encode(), refdir.encode(), p(rdif), C.byref(hi), C.byref(lo), C.byref(rw)) == 0
+        names = sorted(os.listdir(refdir))
+        assert names == [f"reads.fq_k={k}_FG.pgm", f"reads.fq_k={k}_FG_dif.pgm", f"reads.fq_k={k}_QQ.pgm"]
+        for n in names:
+            assert open(os.path.join(refdir, n), "rb").read() == (out / n).read_bytes(), n
+        txt = (out / f"reads.fq.chaos.k{k}.diff.txt").read_text()
+        assert f"Interval of variation of diff matrix values = [{hi.value}, {lo.value}]" in txt
+    finally:
+        shutil.rmtree(work, ignore_errors=True)
+
+
 FILTER_ARGS = ["--read-length-range", "50,", "--read-quality-range", "20,", "--max-N", "5"]
 
 
