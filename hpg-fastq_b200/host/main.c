@@ -18,6 +18,7 @@
  */
 #include "hpgq_host.h"
 
+#include <pthread.h>
 #include <stdlib.h>
 #include <string.h>
 #include <time.h>
@@ -56,6 +57,83 @@ static void usage(const char *exec_name) {
   printf("For more information about a certain command, type %s <command> --help\n", exec_name);
 }
 
+/* Writer thread: the text of a device-composed batch (hpgq_batch_wait_text) is written while the main thread
+ * stages and submits the next batches.  Jobs are executed in order; a slot's pinned text buffer is reused only
+ * after the jobs that point into it are done (wq_wait_for). */
+#define HQ_WQ 16
+typedef struct wjob {
+  hq_writer_t *w;
+  const uint8_t *p;
+  uint64_t n;
+} wjob_t;
+typedef struct wqueue {
+  pthread_t th;
+  pthread_mutex_t mu;
+  pthread_cond_t cv;
+  wjob_t job[HQ_WQ];
+  uint64_t head, tail, done; /* jobs pushed / popped / finished */
+  int started, stop, failed;
+} wqueue_t;
+
+static void *wq_main(void *arg) {
+  wqueue_t *q = (wqueue_t *)arg;
+  pthread_mutex_lock(&q->mu);
+  for (;;) {
+    while (q->tail == q->head && !q->stop) pthread_cond_wait(&q->cv, &q->mu);
+    if (q->tail == q->head) break;
+    const wjob_t j = q->job[q->tail % HQ_WQ];
+    q->tail++;
+    pthread_mutex_unlock(&q->mu);
+    const int bad = hq_writer_put_raw(j.w, j.p, j.n);
+    pthread_mutex_lock(&q->mu);
+    if (bad) q->failed = 1;
+    q->done++;
+    pthread_cond_broadcast(&q->cv);
+  }
+  pthread_mutex_unlock(&q->mu);
+  return NULL;
+}
+
+static int wq_start(wqueue_t *q) {
+  memset(q, 0, sizeof *q);
+  pthread_mutex_init(&q->mu, NULL);
+  pthread_cond_init(&q->cv, NULL);
+  if (pthread_create(&q->th, NULL, wq_main, q)) return -1;
+  q->started = 1;
+  return 0;
+}
+
+/* returns the id to wait for before the memory of this job may be reused */
+static uint64_t wq_push(wqueue_t *q, hq_writer_t *w, const uint8_t *p, uint64_t n) {
+  pthread_mutex_lock(&q->mu);
+  while (q->head - q->done >= HQ_WQ) pthread_cond_wait(&q->cv, &q->mu);
+  q->job[q->head % HQ_WQ] = (wjob_t){w, p, n};
+  const uint64_t id = ++q->head;
+  pthread_cond_broadcast(&q->cv);
+  pthread_mutex_unlock(&q->mu);
+  return id;
+}
+
+static int wq_wait_for(wqueue_t *q, uint64_t id) {
+  if (!q->started) return 0;
+  pthread_mutex_lock(&q->mu);
+  while (q->done < id) pthread_cond_wait(&q->cv, &q->mu);
+  const int bad = q->failed;
+  pthread_mutex_unlock(&q->mu);
+  return bad;
+}
+
+static int wq_finish(wqueue_t *q) {
+  if (!q->started) return 0;
+  pthread_mutex_lock(&q->mu);
+  q->stop = 1;
+  pthread_cond_broadcast(&q->cv);
+  pthread_mutex_unlock(&q->mu);
+  pthread_join(q->th, NULL);
+  q->started = 0;
+  return q->failed;
+}
+
 typedef struct run {
   hq_options_t *o;
   hq_reader_t *reader;
@@ -69,6 +147,8 @@ typedef struct run {
   int device_parse;      /* records are cut on the GPU until a chunk is handed back */
   uint64_t text_budget;  /* bytes of FASTQ text per device-parsed batch */
   uint64_t n_text_batches, n_host_batches;
+  wqueue_t wq;
+  uint64_t wq_id[HQ_MAX_GPUS][HQ_SLOTS]; /* last writer job that reads the slot's text buffer */
 } run_t;
 
 /* the pinned SoA arrays are only needed by the host reader: with the device parser they are allocated when (if)
@@ -109,6 +189,10 @@ static int consume(run_t *r, int g, int s) {
     /* device-parsed batch: the output records were composed on the GPU, the consumer only writes them */
     const uint8_t *text = NULL;
     uint64_t pbytes = 0, fbytes = 0;
+    if (wq_wait_for(&r->wq, r->wq_id[g][s])) { /* the slot's text buffer is about to be overwritten */
+      fprintf(stderr, "\nFATAL: write error on the output FASTQ files\n");
+      return 1;
+    }
     if ((rc = hpgq_batch_wait_text(r->ctx[g], s, &res, &text, &pbytes, &fbytes))) return die_hpgq("hpgq_batch_wait_text", rc);
     r->busy[g][s] = 0;
     r->num_reads += res.n_reads;
@@ -118,11 +202,22 @@ static int consume(run_t *r, int g, int s) {
       r->num_passed += res.n_passed;
       r->num_failed += res.n_failed;
     }
-    if (hq_writer_put_raw(r->w_pass, text, pbytes) || (fbytes && (!r->w_fail || hq_writer_put_raw(r->w_fail, text + pbytes, fbytes)))) {
-      fprintf(stderr, "\nFATAL: write error on the output FASTQ files\n");
+    if (fbytes && !r->w_fail) {
+      fprintf(stderr, "\nFATAL: failed reads without a failed.fq\n");
       return 1;
     }
+    if (!r->wq.started && wq_start(&r->wq)) {
+      fprintf(stderr, "\nFATAL: cannot start the writer thread\n");
+      return 1;
+    }
+    if (pbytes) r->wq_id[g][s] = wq_push(&r->wq, r->w_pass, text, pbytes);
+    if (fbytes) r->wq_id[g][s] = wq_push(&r->wq, r->w_fail, text + pbytes, fbytes);
     return 0;
+  }
+  /* host-parsed batch: written here, after whatever the writer thread still holds (same files, same order) */
+  if (wq_wait_for(&r->wq, r->wq.head)) {
+    fprintf(stderr, "\nFATAL: write error on the output FASTQ files\n");
+    return 1;
   }
   rc = hpgq_batch_wait(r->ctx[g], s, &res);
   if (rc) return die_hpgq("hpgq_batch_wait", rc);
@@ -309,6 +404,10 @@ static int run_command(hq_options_t *o) {
 
   const double t1 = now_s();
   if (run_pipeline(r)) goto out;
+  if (wq_finish(&r->wq)) {
+    fprintf(stderr, "\nFATAL: write error on the output FASTQ files\n");
+    goto out;
+  }
   const double t2 = now_s();
 
   if (r->w_pass && hq_writer_close(r->w_pass)) {
@@ -394,6 +493,7 @@ static int run_command(hq_options_t *o) {
   }
   status = 0;
 out:
+  wq_finish(&r->wq);
   if (r->w_pass) hq_writer_close(r->w_pass);
   if (r->w_fail) hq_writer_close(r->w_fail);
   for (int g = 0; g < HQ_MAX_GPUS; g++) {
