@@ -13,6 +13,7 @@
 
 #include <errno.h>
 #include <fcntl.h>
+#include <pthread.h>
 #include <stdlib.h>
 #include <string.h>
 #include <sys/mman.h>
@@ -72,19 +73,81 @@ int hq_reader_scan(hq_reader_t *r, uint32_t *max_line, uint64_t *n_lines) {
   return hq_reader_scan_prefix(r, r->size, max_line, n_lines);
 }
 
+/* One memchr pass over [lo, hi): number of line breaks, first and last break, longest gap between two consecutive
+ * breaks inside the range (as a line length without '\r').  Ranges are scanned by a few threads and stitched. */
+typedef struct scan_part {
+  const uint8_t *data;
+  uint64_t lo, hi;
+  uint64_t n_breaks, first, last, max_inner;
+  pthread_t th;
+} scan_part_t;
+
+static void *scan_range(void *arg) {
+  scan_part_t *p = (scan_part_t *)arg;
+  uint64_t pos = p->lo, prev = UINT64_MAX;
+  p->n_breaks = 0;
+  p->first = p->last = UINT64_MAX;
+  p->max_inner = 0;
+  while (pos < p->hi) {
+    const uint8_t *nl = (const uint8_t *)memchr(p->data + pos, '\n', p->hi - pos);
+    if (!nl) break;
+    const uint64_t e = (uint64_t)(nl - p->data);
+    if (prev == UINT64_MAX) {
+      p->first = e;
+    } else {
+      uint64_t len = e - prev - 1;
+      if (len && p->data[e - 1] == '\r') len--;
+      if (len > p->max_inner) p->max_inner = len;
+    }
+    prev = e;
+    p->n_breaks++;
+    pos = e + 1;
+  }
+  p->last = prev;
+  return NULL;
+}
+
 int hq_reader_scan_prefix(hq_reader_t *r, uint64_t limit, uint32_t *max_line, uint64_t *n_lines) {
-  uint64_t p = 0, lines = 0, mx = 0;
   if (limit > r->size) limit = r->size;
-  while (p < limit) {
-    const uint8_t *nl = (const uint8_t *)memchr(r->data + p, '\n', r->size - p);
-    uint64_t e = nl ? (uint64_t)(nl - r->data) : r->size;
-    uint64_t len = e - p;
-    if (len && r->data[e - 1] == '\r') len--;
-    /* only sequence / quality lines matter for sizing, but header lines are short: the overall maximum is a
-     * safe (never too small) bound */
+  /* a line that starts before `limit` counts in full: extend the range to the end of that line */
+  uint64_t hi = limit;
+  if (hi < r->size && hi > 0) {
+    const uint8_t *nl = (const uint8_t *)memchr(r->data + hi - 1, '\n', r->size - (hi - 1));
+    hi = nl ? (uint64_t)(nl - r->data) + 1 : r->size;
+  }
+  enum { T = 4 };
+  scan_part_t part[T];
+  const int nt = hi >= (1u << 20) ? T : 1;
+  const uint64_t per = (hi + (uint64_t)nt - 1) / (uint64_t)nt;
+  for (int t = 0; t < nt; t++) {
+    part[t].data = r->data;
+    part[t].lo = (uint64_t)t * per < hi ? (uint64_t)t * per : hi;
+    part[t].hi = part[t].lo + per < hi ? part[t].lo + per : hi;
+  }
+  for (int t = 1; t < nt; t++)
+    if (pthread_create(&part[t].th, NULL, scan_range, &part[t])) {
+      scan_range(&part[t]);
+      part[t].th = 0;
+    }
+  scan_range(&part[0]);
+  for (int t = 1; t < nt; t++)
+    if (part[t].th) pthread_join(part[t].th, NULL);
+  uint64_t lines = 0, mx = 0, prev = UINT64_MAX; /* prev: last break seen so far (none: the first line starts at 0) */
+  for (int t = 0; t < nt; t++) {
+    if (!part[t].n_breaks) continue;
+    uint64_t len = prev == UINT64_MAX ? part[t].first : part[t].first - prev - 1;
+    if (len && r->data[part[t].first - 1] == '\r') len--;
+    if (len > mx) mx = len;
+    if (part[t].max_inner > mx) mx = part[t].max_inner;
+    lines += part[t].n_breaks;
+    prev = part[t].last;
+  }
+  const uint64_t tail_from = prev == UINT64_MAX ? 0 : prev + 1;
+  if (tail_from < hi) { /* last line without a line break */
+    uint64_t len = hi - tail_from;
+    if (r->data[hi - 1] == '\r') len--;
     if (len > mx) mx = len;
     lines++;
-    p = e + 1;
   }
   if (mx > 0xFFFFFFF0ull) return -1;
   *max_line = (uint32_t)mx;

@@ -163,6 +163,36 @@ def test_text_chunks_end_on_record_boundaries(q, tmp_path, eol):
             assert off + ln == len(data) or (off + ln) in starts
 
 
+@pytest.mark.parametrize("final_eol", [True, False])
+def test_scan_is_stitched_across_thread_ranges(tmp_path, final_eol):
+    """hq_reader_scan splits files above 1 MB over four threads: lines that straddle a range boundary (also one
+    much longer than a range) must still be measured whole, '\\r' excluded."""
+    rng = np.random.default_rng(3)
+    lines = [b"x" * int(n) for n in rng.integers(0, 300, size=20000)]
+    lines[7000] = b"y" * 900_000          # longer than a quarter of the file
+    lines[12000] = b"z" * 1234 + b"\r"     # CRLF line: the '\\r' does not count
+    lines[-1] = b"w" * 77
+    data = b"\n".join(lines) + (b"\n" if final_eol else b"")
+    assert len(data) > (1 << 20)
+    path = str(tmp_path / "scan.txt")
+    with open(path, "wb") as f:
+        f.write(data)
+    r = hb.Reader(path)
+    mx, n = r.scan()
+    r.close()
+    assert mx == 900_000 and n == len(lines)
+    # boundaries of the four ranges fall inside lines: move the long line around
+    for where in (0, 3000, 19999):
+        ls = [b"x" * int(k) for k in rng.integers(0, 300, size=20000)]
+        ls[where] = b"q" * 700_001
+        with open(path, "wb") as f:
+            f.write(b"\r\n".join(ls) + b"\r\n")
+        r = hb.Reader(path)
+        mx, n = r.scan()
+        r.close()
+        assert mx == 700_001 and n == 20000
+
+
 def test_writer_matches_record_layout(q, tmp_path):
     """header, sequence, '+', quality, each newline-terminated, in the order given by src."""
     seq, qual, idx = synth_reads(q, 300, seed=11)
