@@ -80,7 +80,12 @@ class ClockSampler:
             return
         self.period = period
         self.t = threading.Thread(target=self._run, daemon=True)
-        self.t.start()
+
+    def start(self):
+        """NVML was initialised in __init__ (tens of ms, and not the same on every rank): only the thread starts here,
+        after the barrier that opens the timed region."""
+        if self.nv is not None:
+            self.t.start()
 
     def _run(self):
         nv = self.nv
@@ -157,6 +162,32 @@ def run_reference(args):
     emit(line)
 
 
+def bind_to_gpu_numa_node(local):
+    """Pins this rank's threads to the CPUs of the NUMA node its GPU hangs off, BEFORE any pinned memory is
+    allocated: first-touch then places the pinned batches next to the GPU's PCIe root, so that the H2D copies of
+    eight ranks do not all stream out of one socket's DRAM (and across the inter-socket link)."""
+    try:
+        import torch
+        pr = torch.cuda.get_device_properties(local)
+        bdf = f"{pr.pci_domain_id:04x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0"
+        with open(f"/sys/bus/pci/devices/{bdf}/numa_node") as f:
+            node = int(f.read().strip())
+        if node < 0:
+            return None
+        with open(f"/sys/devices/system/node/node{node}/cpulist") as f:
+            cpus = set()
+            for part in f.read().strip().split(","):
+                a, _, b = part.partition("-")
+                cpus.update(range(int(a), int(b or a) + 1))
+        allowed = cpus & os.sched_getaffinity(0)
+        if allowed:
+            os.sched_setaffinity(0, allowed)
+            return node
+    except Exception:
+        pass
+    return None
+
+
 _REAL_STDOUT = None
 
 
@@ -193,6 +224,7 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a B200: there is no CPU fallback (use --impl reference for the CPU path)")
     torch.cuda.set_device(local)
+    numa_node = bind_to_gpu_numa_node(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
@@ -256,8 +288,9 @@ def main():
 
     for _ in range(args.warmup):
         step(False)
-    barrier()
     sampler = ClockSampler(local)
+    barrier()
+    sampler.start()
     l0 = ctx.launch_count()
     ev0 = torch.cuda.Event(enable_timing=True)
     ev1 = torch.cuda.Event(enable_timing=True)
@@ -356,7 +389,8 @@ def main():
         dt = float(tt.item())
         e2e = {"value": done * world / dt, "unit": "reads/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                "ms_per_step": dt * 1e3, "h2d_gbs_per_gpu": h2d / dt / 1e9, "batch_reads": EB,
-               "pinned_pool_batches": len(pool), "timing": "wall clock between device synchronisations, max over ranks"}
+               "pinned_pool_batches": len(pool), "numa_node_of_rank0": numa_node,
+               "timing": "wall clock between device synchronisations, max over ranks"}
         ectx.close()
         for _, ps, pq, pi, _ in pool:
             q.free_pinned(ps)
