@@ -354,23 +354,50 @@ def main():
         ectx.set_params(par)
         n_sub = (n_reads + EB - 1) // EB
 
+        # Batches are dealt by TICKET: a rank draws the next batch number when one of its two slots is free, so a GPU
+        # whose PCIe uplink is shared (profiles/h2d_probe_n8_r1l.log: with eight ranks copying, GPUs 0-3 get 23.8 GB/s
+        # each and GPUs 4-7 35.5) takes fewer batches instead of holding the others up. The job is still
+        # world x n_sub batches per step; at N = 1 the counter is local.
+        store = dist.distributed_c10d._get_default_store() if world > 1 else None
+        total_sub = n_sub * world
+        step_no = [0]
+
         def e2e_step():
             ectx.counters_reset()
+            key = f"hpgq_e2e_ticket_{step_no[0]}"
+            step_no[0] += 1
+            local_next = [0]
+
+            def draw():
+                if store is None:
+                    local_next[0] += 1
+                    return local_next[0] - 1
+                return store.add(key, 1) - 1
+
             h2d = d2h = 0
             done = 0
-            for i in range(n_sub):
+            busy = [False, False]
+            i = 0
+            while True:
                 slot = i % 2
-                if i >= 2:
+                if busy[slot]:
+                    r = ectx.wait(slot)
+                    busy[slot] = False
+                    done += r["n_reads"]
+                    d2h += r["n_reads"]
+                t = draw()
+                if t >= total_sub:
+                    break
+                nr, ps, pq, pi, nbytes = pool[t % len(pool)]
+                ectx.submit_raw(nr, ps, pq, pi, slot)
+                busy[slot] = True
+                h2d += 2 * nbytes + (nr + 1) * 4
+                i += 1
+            for slot in ((i % 2), ((i + 1) % 2)):
+                if busy[slot]:
                     r = ectx.wait(slot)
                     done += r["n_reads"]
                     d2h += r["n_reads"]
-                nr, ps, pq, pi, nbytes = pool[i % len(pool)]
-                ectx.submit_raw(nr, ps, pq, pi, slot)
-                h2d += 2 * nbytes + (nr + 1) * 4
-            for i in range(max(n_sub - 2, 0), n_sub):
-                r = ectx.wait(i % 2)
-                done += r["n_reads"]
-                d2h += r["n_reads"]
             c = ectx.counters()
             d2h += c.nbytes
             return done, h2d, d2h
@@ -384,12 +411,22 @@ def main():
         barrier()
         dt = (time.perf_counter() - t0) / e_steps
         tt = torch.tensor([dt], device="cuda", dtype=torch.float64)
+        job = torch.tensor([done, h2d, d2h], device="cuda", dtype=torch.float64)
+        per_rank_reads = [done]
         if world > 1:
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            g = [torch.zeros_like(job) for _ in range(world)]
+            dist.all_gather(g, job)
+            per_rank_reads = [int(x[0].item()) for x in g]
+            job = torch.stack(g).sum(0)
         dt = float(tt.item())
-        e2e = {"value": done * world / dt, "unit": "reads/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-               "ms_per_step": dt * 1e3, "h2d_gbs_per_gpu": h2d / dt / 1e9, "batch_reads": EB,
+        job_reads, job_h2d, job_d2h = (float(x) for x in job.tolist())
+        e2e = {"value": job_reads / dt, "unit": "reads/s", "h2d_bytes_per_step": int(job_h2d / world),
+               "d2h_bytes_per_step": int(job_d2h / world),
+               "ms_per_step": dt * 1e3, "h2d_gbs_per_gpu": job_h2d / world / dt / 1e9, "batch_reads": EB,
                "pinned_pool_batches": len(pool), "numa_node_of_rank0": numa_node,
+               "dealing": "ticket per batch (shared counter); bytes per step are the mean over ranks",
+               "reads_per_rank_last_step": per_rank_reads,
                "timing": "wall clock between device synchronisations, max over ranks"}
         ectx.close()
         for _, ps, pq, pi, _ in pool:
