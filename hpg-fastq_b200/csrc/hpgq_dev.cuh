@@ -273,6 +273,21 @@ HQ_DI void hq_mbar_wait_backoff(uint64_t *bar, uint32_t parity) {
     __nanosleep(100);
   }
 }
+// try_wait with a suspend-time hint (ns): the thread is parked by the hardware until the phase completes or the
+// hint runs out, instead of polling
+HQ_DI void hq_mbar_wait_hint(uint64_t *bar, uint32_t parity, uint32_t hint_ns) {
+  const uint32_t a = hq_smem_u32(bar);
+  uint32_t ok;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(a), "r"(parity), "r"(hint_ns)
+        : "memory");
+  } while (!ok);
+}
 // 1-D bulk async copy global -> shared (TMA engine, SASS UBLKCP); 16-byte aligned, size % 16 == 0
 HQ_DI void hq_bulk_g2s(void *dst_smem, const void *src_gmem, uint32_t bytes, uint64_t *bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(

@@ -65,6 +65,11 @@ bool pick_geom(uint32_t max_len, uint32_t n_reads, int sm_count, size_t smem_lim
     if ((size_t)cand * max_len >= tile_bytes) break;  // big enough to amortise the barriers
   }
   if (!RT) return false;
+  // developer knob: reads per tile forced (a multiple of 4 that fits the stage budget), e.g. 252 with HQ_PRANK
+  const uint32_t force = env_u32("HPGQ_RT", 0, 0, 65535u);
+  if (force && force % 4u == 0u &&
+      idx_cap_bytes(force) + 2ull * ((((size_t)force * max_len + 48u + pad) + 127u) & ~127ull) <= budget)
+    RT = force;
   // small batches: keep at least ~2 tiles per SM so the grid is balanced
   const uint32_t want_tiles = (uint32_t)sm_count * 2u;
   while (RT > unit && (n_reads + RT - 1u) / RT < want_tiles) RT -= unit;

@@ -42,6 +42,16 @@ constexpr int NSMAX = 8;                 // pipeline stages are a launch paramet
 #ifndef HQ_TICKET
 #define HQ_TICKET 0
 #endif
+// HQ_PRANK = 1: the three consumer warps that share a scheduler with the producer own the first chunks of every
+// round, i.e. the extra chunks of a tile whose chunk count is not a multiple of the consumer warps (HPGQ_RT=252: 63
+// chunks = 4 per warp + one more for those three).  HQ_PRODHINT = ns: the producer parks on the `empty` barrier with a
+// try_wait suspend-time hint instead of polling with nanosleep.
+#ifndef HQ_PRANK
+#define HQ_PRANK 0
+#endif
+#ifndef HQ_PRODHINT
+#define HQ_PRODHINT 0
+#endif
 #ifndef HQ_NCW
 #define HQ_NCW (HQ_NOPROD ? 16 : 15)
 #endif
