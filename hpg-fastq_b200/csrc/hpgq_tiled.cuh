@@ -52,6 +52,11 @@ constexpr int NSMAX = 8;                 // pipeline stages are a launch paramet
 #ifndef HQ_PRODHINT
 #define HQ_PRODHINT 0
 #endif
+// HQ_IDXPF = 1: a chunk's two read offsets are loaded from the stage one chunk ahead (two registers).  Measured on
+// B200: 3 874 GB/s against 3 891 without (profiles/sweep_r1m.log), and the K = 5 FULL kernels spill; off.
+#ifndef HQ_IDXPF
+#define HQ_IDXPF 0
+#endif
 #ifndef HQ_NCW
 #define HQ_NCW (HQ_NOPROD ? 16 : 15)
 #endif
