@@ -57,6 +57,11 @@ constexpr int NSMAX = 8;                 // pipeline stages are a launch paramet
 #ifndef HQ_IDXPF
 #define HQ_IDXPF 0
 #endif
+// HQ_ACC8S = 1: the 8-bit level of the per-position ladder (4 K words per thread, touched once every 15 chunks) lives in
+// shared memory instead of registers -- the registers it frees are what a fifth warp per scheduler (HQ_NCW = 19) needs.
+#ifndef HQ_ACC8S
+#define HQ_ACC8S 0
+#endif
 #ifndef HQ_NCW
 #define HQ_NCW (HQ_NOPROD ? 16 : 15)
 #endif
@@ -76,7 +81,8 @@ constexpr uint32_t SM_GC = SM_QH + 4u * 256u;                // u32 [104]
 constexpr uint32_t SM_SUMQ = SM_GC + 4u * 104u;              // u64 [TAB + 4]
 constexpr uint32_t SM_CNT = SM_SUMQ + 8u * (TAB + 4);        // u32 [TAB + 4]: reads covering position j
 constexpr uint32_t SM_RECS = SM_CNT + 4u * (TAB + 4);        // uint4 [NCW][32]
-constexpr uint32_t SM_STAGES = (SM_RECS + 16u * NCW * 32u + 127u) & ~127u;
+constexpr uint32_t SM_ACC8 = SM_RECS + 16u * NCW * 32u;     // u32 [4 * KMAX][THREADS] when HQ_ACC8S
+constexpr uint32_t SM_STAGES = (SM_ACC8 + (HQ_ACC8S ? 16u * KMAX * THREADS : 0u) + 127u) & ~127u;
 static_assert(SM_SUMQ % 8 == 0, "sumq must be 8-byte aligned");
 static_assert(SM_RECS % 16 == 0, "records must be 16-byte aligned");
 
