@@ -58,7 +58,10 @@ constexpr int NSMAX = 8;                 // pipeline stages are a launch paramet
 #define HQ_IDXPF 0
 #endif
 // HQ_ACC8S = 1: the 8-bit level of the per-position ladder (4 K words per thread, touched once every 15 chunks) lives in
-// shared memory instead of registers -- the registers it frees are what a fifth warp per scheduler (HQ_NCW = 19) needs.
+// shared memory instead of registers -- the registers it frees are what a fifth warp per scheduler (HQ_NCW = 19) needs:
+// 96 registers, no spill in the FULL = 0 kernels.  Measured on B200 (profiles/sweep_r1n.log): 15 warps 3 890 GB/s (as
+// without), 19 warps 3 827, 18 warps 3 684 -- the columns take 51 KB from the ring, a tile is then 228 reads = 3 chunks
+// per warp and lasts about as long as its own load, so the fifth warp waits for data instead of hiding latency.  Off.
 #ifndef HQ_ACC8S
 #define HQ_ACC8S 0
 #endif
