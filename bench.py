@@ -358,8 +358,13 @@ def main():
         # whose PCIe uplink is shared (profiles/h2d_probe_n8_r1l.log: with eight ranks copying, GPUs 0-3 get 23.8 GB/s
         # each and GPUs 4-7 35.5) takes fewer batches instead of holding the others up. The job is still
         # world x n_sub batches per step; at N = 1 the counter is local.
-        store = dist.distributed_c10d._get_default_store() if world > 1 else None
-        total_sub = n_sub * world
+        store = None
+        if world > 1:
+            try:
+                store = dist.distributed_c10d._get_default_store()
+            except Exception:
+                store = None  # no shared counter: every rank takes its own n_sub batches (equal shares)
+        total_sub = n_sub * world if store is not None else n_sub
         step_no = [0]
 
         def e2e_step():
@@ -425,7 +430,8 @@ def main():
                "d2h_bytes_per_step": int(job_d2h / world),
                "ms_per_step": dt * 1e3, "h2d_gbs_per_gpu": job_h2d / world / dt / 1e9, "batch_reads": EB,
                "pinned_pool_batches": len(pool), "numa_node_of_rank0": numa_node,
-               "dealing": "ticket per batch (shared counter); bytes per step are the mean over ranks",
+               "dealing": ("ticket per batch (shared counter); bytes per step are the mean over ranks"
+                           if store is not None or world == 1 else "equal shares (no shared counter)"),
                "reads_per_rank_last_step": per_rank_reads,
                "timing": "wall clock between device synchronisations, max over ranks"}
         ectx.close()
