@@ -126,7 +126,8 @@ def cpu_leg(q, ob, ctx, cfg, n_sample, steps, warmup, threads=0):
     else:
         seq, qual, idx = q.synth_host(cfg, 0, n_sample)
     lay = ob.layout(q.Layout, 160)
-    cores = ob.max_threads() if threads <= 0 else threads
+    # torchrun exports OMP_NUM_THREADS=1: take the core count from the affinity mask, never from OpenMP's default
+    cores = len(os.sched_getaffinity(0)) if threads <= 0 else threads
     times = []
     for i in range(warmup + steps):
         t0 = time.perf_counter()
@@ -275,7 +276,7 @@ def main():
                 ctx.sync(sl)
                 if collect:
                     kernel_ms.append((ctx.last_kernel_ms(sl), inflight[sl]))
-            ctx.submit_device(b, sl)
+            ctx.submit_device(b, sl, uniform=True)
             inflight[sl] = b.n_reads
         for sl in range(NSLOT):
             if inflight[sl] is not None:

@@ -35,6 +35,7 @@ struct hpgq_slot {
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   bool busy = false, timed = false;
   bool dev_batch = false;
+  bool uniform = false;  // every read of the current batch has max_len bases (proven or stated by the caller)
   uint32_t n_reads = 0, max_len = 0;
   uint64_t n_bytes = 0;
   uint32_t work = 0;
@@ -50,7 +51,7 @@ struct hpgq_slot {
   // outputs
   uint8_t *d_mask = nullptr, *h_mask = nullptr;
   hpgq_trim_t *d_trim = nullptr, *h_trim = nullptr;
-  uint32_t *d_maxlen = nullptr, *h_small = nullptr; // h_small: [0]=maxlen [4..7]=totals (pinned)
+  uint32_t *d_maxlen = nullptr, *h_small = nullptr; // h_small: [0..2]=max/min length, order flag [4..7]=totals [8..9]=HPGQ_S_BAD_BATCH (pinned)
   hq_compact_bufs cb = {};
   uint64_t cb_reads = 0, cb_bytes = 0;
   uint8_t *h_out_seq = nullptr, *h_out_qual = nullptr;
@@ -296,7 +297,10 @@ extern "C" int hpgq_counters_download(hpgq_ctx_t *ctx, uint64_t *dst, size_t n_w
   CK(cudaDeviceSynchronize());
   CK(cudaMemcpy(dst, ctx->d_ctr, ctx->lay.offset[HPGQ_SEC_COUNT] * 8, cudaMemcpyDeviceToHost));
   dst[HPGQ_S_BATCHES] = ctx->batches;
-  return hpgq_counters_finalize_host(&ctx->lay, dst);
+  int rc = hpgq_counters_finalize_host(&ctx->lay, dst);
+  if (rc == HPGQ_OK && dst[HPGQ_S_BAD_BATCH])
+    return fail_msg(HPGQ_ERR_INVALID, "a batch broke the length statement it was submitted with (hpgq_batch_t.reserved): counters are invalid");
+  return rc;
 }
 
 extern "C" int hpgq_counters_device_ptr(hpgq_ctx_t *ctx, uint64_t **dptr, size_t *n_words) {

@@ -38,16 +38,15 @@ struct hq_kargs {
   uint32_t stage_bytes; // capacity of one seq (and one qual) stage buffer
   uint32_t n_tiles;
   uint32_t n_stages;    // depth of the shared-memory ring
-  // multipliers the compiler cannot see through (1, 2^20, 2^24): `x * one + y`, `umulhi(x, p20) + y` stay
-  // IMAD / IMAD.HI on the FMA pipe instead of being strength-reduced to IADD3 / SHF / LEA.HI on the ALU
-  // pipe, which is the busiest unit of the tiled kernel (profiles/tiled_r1b_summary.md)
-  uint32_t one, p20, p24;
+  uint32_t uni_len;     // uniform-length kernels: the length every read of the batch has
 };
 
 // launchers (return cudaGetLastError()); `launches` is incremented per kernel launched
 cudaError_t hq_launch_qc_simple(const hq_kargs &a, cudaStream_t st, uint64_t *launches);
 // returns cudaErrorInvalidValue if the batch does not fit the tiled kernel (max read length > 640)
-cudaError_t hq_launch_qc_tiled(hq_kargs a, uint32_t max_len_in_batch, int sm_count, cudaStream_t st,
+// uniform = true: the caller states that every read has exactly max_len_in_batch bases (the kernel verifies it and
+// raises HPGQ_S_BAD_BATCH otherwise); the aligned-word variant is used when the geometry allows it
+cudaError_t hq_launch_qc_tiled(hq_kargs a, uint32_t max_len_in_batch, bool uniform, int sm_count, cudaStream_t st,
                                uint64_t *launches);
 bool hq_tiled_supports(uint32_t max_len_in_batch, uint32_t work);
 // vectorised any-length path (hpgq_group.cu): decisions + per-read histograms, then per-position tables
@@ -56,6 +55,7 @@ cudaError_t hq_launch_qc_group(const hq_kargs &a, uint32_t max_len_in_batch, int
 cudaError_t hq_launch_pos(const hq_kargs &a, uint32_t max_len_in_batch, int sm_count, cudaStream_t st,
                           uint64_t *launches);
 cudaError_t hq_launch_kmers_cg(const hq_kargs &a, uint32_t max_len_in_batch, cudaStream_t st, uint64_t *launches);
+// d_out[0] = longest read, d_out[1] = shortest read, d_out[2] = 1 if some offset decreases
 cudaError_t hq_launch_maxlen(const uint32_t *idx, uint32_t n, uint32_t *d_out, cudaStream_t st, uint64_t *launches);
 
 struct hq_compact_bufs {
@@ -72,7 +72,7 @@ cudaError_t hq_launch_synth(const hpgq_synth_cfg_t &cfg, uint64_t first_read, ui
                             uint8_t *d_qual, const uint32_t *d_idx, cudaStream_t st, uint64_t *launches);
 
 // ------------------------------------------------------------------ device FASTQ text parser (hpgq_parse.cu)
-enum { HQ_PINFO_LINES = 0, HQ_PINFO_READS, HQ_PINFO_MAXLEN, HQ_PINFO_BAD, HQ_PINFO_BASES, HQ_PINFO_STATUS, HQ_PINFO_COUNT = 8 };
+enum { HQ_PINFO_LINES = 0, HQ_PINFO_READS, HQ_PINFO_MAXLEN, HQ_PINFO_BAD, HQ_PINFO_BASES, HQ_PINFO_STATUS, HQ_PINFO_MINLEN, HQ_PINFO_COUNT = 8 };
 // bits of info[HQ_PINFO_STATUS] = hpgq_text_info_t.status (include/hpg_fastq_cuda.h HPGQ_TEXT_*)
 enum { HQ_PSTAT_LINES = 1, HQ_PSTAT_RECORD = 2, HQ_PSTAT_TOO_MANY = 4 };
 struct hq_parse_bufs {

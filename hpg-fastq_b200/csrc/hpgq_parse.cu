@@ -171,7 +171,7 @@ __global__ void __launch_bounds__(PT) hq_parse_cut(const uint8_t *text, const ui
   if (R > cap_reads || lines > cap_lines) R = 0;  // nothing below may index past the arrays
   uint32_t rb, re;
   hq_parse_range(R, &rb, &re);
-  uint32_t sum = 0, mx = 0, bad = 0xFFFFFFFFu;
+  uint32_t sum = 0, mx = 0, mn = 0xFFFFFFFFu, bad = 0xFFFFFFFFu;
   for (uint32_t r = rb + threadIdx.x; r < re; r += PT) {
     const uint32_t hb = r ? nl[4u * r - 1u] + 1u : 0u;
     uint32_t he = nl[4u * r], se = nl[4u * r + 1u], pe = nl[4u * r + 2u], qe = nl[4u * r + 3u];
@@ -190,14 +190,17 @@ __global__ void __launch_bounds__(PT) hq_parse_cut(const uint8_t *text, const ui
     hdr_len[r] = he - hb;
     sum += L;
     mx = max(mx, L);
+    mn = min(mn, L);
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
     mx = max(mx, __shfl_xor_sync(0xFFFFFFFFu, mx, o));
+    mn = min(mn, __shfl_xor_sync(0xFFFFFFFFu, mn, o));
     bad = min(bad, __shfl_xor_sync(0xFFFFFFFFu, bad, o));
   }
   if ((threadIdx.x & 31u) == 0) {
     if (mx) atomicMax(&info[HQ_PINFO_MAXLEN], mx);
+    atomicMin(&info[HQ_PINFO_MINLEN], mn);
     if (bad != 0xFFFFFFFFu) {
       atomicMin(&info[HQ_PINFO_BAD], bad);
       atomicOr(&info[HQ_PINFO_STATUS], HQ_PSTAT_RECORD);
@@ -342,6 +345,7 @@ cudaError_t hq_launch_parse(const hq_parse_bufs &b, int sm_count, cudaStream_t s
   cudaError_t e = cudaMemsetAsync(b.info, 0, HQ_PINFO_COUNT * 4, st);
   if (e != cudaSuccess) return e;
   e = cudaMemsetAsync(b.info + HQ_PINFO_BAD, 0xFF, 4, st);
+  if (e == cudaSuccess) e = cudaMemsetAsync(b.info + HQ_PINFO_MINLEN, 0xFF, 4, st);
   if (e != cudaSuccess) return e;
   if (n_tiles) {
     hq_parse_count<<<min((uint32_t)grid, n_tiles), PT, 0, st>>>(b.text, n, n_tiles, b.tile_cnt);

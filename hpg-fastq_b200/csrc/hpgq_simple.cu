@@ -418,13 +418,26 @@ __global__ void __launch_bounds__(K5_THREADS, 1) hq_k5pos_kernel(hq_kargs a, uin
 }
 
 // ---------------------------------------------------------------- max read length of a batch
+// out[0] = longest read, out[1] = shortest read, out[2] = 1 if some offset is smaller than its predecessor
 __global__ void hq_maxlen_kernel(const uint32_t *idx, uint32_t n, uint32_t *out) {
-  uint32_t m = 0;
-  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
-    m = max(m, idx[i + 1] - idx[i]);
+  uint32_t m = 0, lo = 0xFFFFFFFFu, dec = 0;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const uint32_t a = idx[i], b = idx[i + 1];
+    if (b < a) dec = 1u;
+    m = max(m, b - a);
+    lo = min(lo, b - a);
+  }
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xFFFFFFFFu, m, o));
-  if ((threadIdx.x & 31) == 0 && m) atomicMax(out, m);
+  for (int o = 16; o > 0; o >>= 1) {
+    m = max(m, __shfl_xor_sync(0xFFFFFFFFu, m, o));
+    lo = min(lo, __shfl_xor_sync(0xFFFFFFFFu, lo, o));
+    dec |= __shfl_xor_sync(0xFFFFFFFFu, dec, o);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    if (m) atomicMax(out, m);
+    atomicMin(out + 1, lo);
+    if (dec) atomicExch(out + 2, 1u);
+  }
 }
 
 // ---------------------------------------------------------------- synthetic reads (thread per read)
@@ -496,7 +509,8 @@ cudaError_t hq_launch_kmers_cg(const hq_kargs &a0, uint32_t max_len_in_batch, cu
 }
 
 cudaError_t hq_launch_maxlen(const uint32_t *idx, uint32_t n, uint32_t *d_out, cudaStream_t st, uint64_t *launches) {
-  cudaError_t e = cudaMemsetAsync(d_out, 0, sizeof(uint32_t), st);
+  cudaError_t e = cudaMemsetAsync(d_out, 0, 3 * sizeof(uint32_t), st);
+  if (e == cudaSuccess) e = cudaMemsetAsync(d_out + 1, 0xFF, sizeof(uint32_t), st);
   if (e != cudaSuccess || n == 0) return e;
   uint32_t blocks = (n + 255u) / 256u;
   if (blocks > 148u * 8u) blocks = 148u * 8u;

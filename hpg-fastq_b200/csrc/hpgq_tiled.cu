@@ -29,19 +29,23 @@ uint32_t env_u32(const char *name, uint32_t dflt, uint32_t lo, uint32_t hi) {
   return x < (long)lo ? lo : (x > (long)hi ? hi : (uint32_t)x);
 }
 
-bool pick_geom(uint32_t max_len, uint32_t n_reads, int sm_count, size_t smem_limit, hq_geom *out) {
+// uniform = true: geometry for the aligned-word kernel.  A read may start at byte phase 0..3 of its first word, so
+// the frame is 3 bytes longer; the group count must keep the phase constant ((32 / G) * len % 4 == 0) and only a
+// lane's first and last word may be partial (len >= 4 (K - 1) G).
+bool pick_geom(uint32_t max_len, bool uniform, uint32_t n_reads, int sm_count, size_t smem_limit, hq_geom *out) {
   // two stages of the largest tiles that fit (300 reads of 150 bp) beat three stages of 180 reads by 2.3 %: the
   // per-tile entry / exit costs a warp about a fifth of an iteration (profiles/tiled_r1i_summary.md)
   const uint32_t NS = env_u32("HPGQ_STAGES", 2, 2, NSMAX);
   const uint32_t tile_bytes = env_u32("HPGQ_TILE_BYTES", 46 * 1000, 1024, 64 * 1024);
   if (max_len == 0) max_len = 1;
-  const uint32_t words = (max_len + 3u) / 4u;
+  const uint32_t words = (max_len + (uniform ? 6u : 3u)) / 4u;
   double best = -1.0;
   int bK = 0, bG = 0;
   for (const geom_entry &ge : kGeoms) {
     if ((uint32_t)(ge.K * ge.G) < words) continue;
     if (4 * ge.K * ge.G <= 256 && max_len > 255u) continue;  // packed group sum holds 8-bit base counts
     const uint32_t NG = 32u / (uint32_t)ge.G;
+    if (uniform && (((NG * max_len) & 3u) != 0u || max_len < 4u * (uint32_t)((ge.K - 1) * ge.G))) continue;
     // useful word slots per warp iteration / 32*K slots issued, ties go to the larger K (less per-read overhead)
     const double eff = ((double)words * NG) / (32.0 * ge.K) + 0.002 * ge.K;
     if (eff > best) {
@@ -52,7 +56,9 @@ bool pick_geom(uint32_t max_len, uint32_t n_reads, int sm_count, size_t smem_lim
   }
   if (!bK) return false;
   const uint32_t NGB = NCW * (32u / (uint32_t)bG);
-  const uint32_t pad = 4u * bK * bG + 64u;
+  // bytes a lane may touch past the last read of a tile: one frame; the uniform loop also addresses the reads of
+  // lane groups that have none left in the tile (32 / G + 1 reads further)
+  const uint32_t pad = 4u * bK * bG + 64u + (uniform ? (32u / (uint32_t)bG + 1u) * max_len : 0u);
   // reads per tile: a multiple of lcm(NGB, 4) that fits the per-stage budget
   uint32_t unit = NGB;
   while (unit % 4u) unit += NGB;
@@ -83,8 +89,9 @@ bool pick_geom(uint32_t max_len, uint32_t n_reads, int sm_count, size_t smem_lim
 }
 
 template <int K, int G>
-cudaError_t launch_kg(const hq_kargs &a, bool full, int grid, uint32_t smem, cudaStream_t st) {
-  return full ? launch_inst<K, G, true>(a, grid, smem, st) : launch_inst<K, G, false>(a, grid, smem, st);
+cudaError_t launch_kg(const hq_kargs &a, bool full, bool uni, int grid, uint32_t smem, cudaStream_t st) {
+  if (uni) return full ? launch_inst<K, G, true, true>(a, grid, smem, st) : launch_inst<K, G, false, true>(a, grid, smem, st);
+  return full ? launch_inst<K, G, true, false>(a, grid, smem, st) : launch_inst<K, G, false, false>(a, grid, smem, st);
 }
 
 }  // namespace
@@ -94,30 +101,31 @@ bool hq_tiled_supports(uint32_t max_len_in_batch, uint32_t work) {
   return max_len_in_batch <= (uint32_t)(4 * KMAX * 32);
 }
 
-cudaError_t hq_launch_qc_tiled(hq_kargs a, uint32_t max_len_in_batch, int sm_count, cudaStream_t st,
+cudaError_t hq_launch_qc_tiled(hq_kargs a, uint32_t max_len_in_batch, bool uniform, int sm_count, cudaStream_t st,
                                uint64_t *launches) {
   if (a.n_reads == 0) return cudaSuccess;
   hq_geom gm;
-  if (!hq_tiled_supports(max_len_in_batch, a.work) ||
-      !pick_geom(max_len_in_batch, a.n_reads, sm_count, 227 * 1024, &gm))
-    return cudaErrorInvalidValue;
+  if (!hq_tiled_supports(max_len_in_batch, a.work)) return cudaErrorInvalidValue;
+  // HPGQ_NO_UNI: developer / test knob that keeps uniform batches on the general kernel
+  bool uni = uniform && max_len_in_batch > 0 && !getenv("HPGQ_NO_UNI");
+  if (uni && !pick_geom(max_len_in_batch, true, a.n_reads, sm_count, 227 * 1024, &gm)) uni = false;
+  if (!uni && !pick_geom(max_len_in_batch, false, a.n_reads, sm_count, 227 * 1024, &gm)) return cudaErrorInvalidValue;
   a.RT = gm.RT;
   if (getenv("HPGQ_DEBUG_LOADONLY")) a.work |= 0x8000u;  // developer probe: ring traffic without the arithmetic
   a.n_stages = gm.NS;
-  a.one = 1u;
-  a.p20 = 1u << 20;
-  a.p24 = 1u << 24;
+  a.uni_len = uni ? max_len_in_batch : 0u;
   a.G = (uint32_t)gm.G;
   a.stage_bytes = gm.stage_bytes;
   a.n_tiles = (a.n_reads + gm.RT - 1u) / gm.RT;
   // every CTA keeps u32 block-private tables: bound the reads a CTA can see (255 * reads < 2^32)
-  int grid = sm_count;
+  // HPGQ_GRID_CAP: test knob -- few CTAs, so that a small batch drives every warp through the in-loop flushes
+  int grid = (int)env_u32("HPGQ_GRID_CAP", (uint32_t)sm_count, 1, (uint32_t)sm_count);
   if ((uint32_t)grid > a.n_tiles) grid = (int)a.n_tiles;
   if ((uint64_t)(a.n_tiles / grid + 1) * gm.RT >= 16000000ull) return cudaErrorInvalidValue;
   const bool full = (a.f_ll > 0) || (a.f_rl > 0) || (a.max_ooq < (int32_t)max_len_in_batch);
   cudaError_t e = cudaErrorInvalidValue;
 #define HQ_CASE(KK, GG) \
-  if (gm.K == KK && gm.G == GG) e = launch_kg<KK, GG>(a, full, grid, gm.smem_bytes, st);
+  if (gm.K == KK && gm.G == GG) e = launch_kg<KK, GG>(a, full, uni, grid, gm.smem_bytes, st);
   HQ_CASE(2, 4) HQ_CASE(3, 4) HQ_CASE(4, 4) HQ_CASE(5, 4) HQ_CASE(5, 5)
   HQ_CASE(3, 8) HQ_CASE(4, 8) HQ_CASE(5, 8)
   HQ_CASE(3, 16) HQ_CASE(4, 16) HQ_CASE(5, 16)

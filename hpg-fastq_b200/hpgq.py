@@ -27,8 +27,9 @@ SEC = {n: i for i, n in enumerate(SEC_NAMES)}
 SEC_COUNT = len(SEC_NAMES)
 SCALAR_NAMES = [
     "NUM_READS", "NUM_PASSED", "NUM_FAILED", "NUM_EDITED", "ACC_LENGTH", "NUM_A", "NUM_C", "NUM_G", "NUM_T",
-    "NUM_N", "MIN_LENGTH", "MAX_LENGTH", "CG_WORDS", "CG_LONG_RUNS", "SLOW_READS", "BATCHES",
+    "NUM_N", "MIN_LENGTH", "MAX_LENGTH", "CG_WORDS", "CG_LONG_RUNS", "SLOW_READS", "BATCHES", "BAD_BATCH",
 ]
+BATCH_UNIFORM = 0x80000000
 S = {n: i for i, n in enumerate(SCALAR_NAMES)}
 
 
@@ -308,6 +309,20 @@ class Ctx:
             "hpgq_dev_download")
         return out
 
+    def dev_upload(self, ptr: int, data: np.ndarray):
+        data = np.ascontiguousarray(data)
+        _ck(self.lib.hpgq_dev_upload(self.h, C.c_void_p(ptr), data.ctypes.data_as(C.c_void_p), C.c_size_t(data.nbytes)),
+            "hpgq_dev_upload")
+
+    def upload_batch(self, seq: np.ndarray, qual: np.ndarray, idx: np.ndarray, max_len: int = 0) -> DeviceBatch:
+        """Host arrays -> a device-resident batch (idx may start anywhere: seq/qual are indexed by idx as given)."""
+        n, nb = len(idx) - 1, int(idx[-1])
+        ds, dq, di = self.dev_alloc(nb + 64), self.dev_alloc(nb + 64), self.dev_alloc((n + 1) * 4 + 64)
+        self.dev_upload(ds, np.asarray(seq[:nb], dtype=np.uint8))
+        self.dev_upload(dq, np.asarray(qual[:nb], dtype=np.uint8))
+        self.dev_upload(di, np.asarray(idx, dtype=np.uint32))
+        return DeviceBatch(n, nb, ds, dq, di, max_len, [ds, dq, di])
+
     def synth_device(self, cfg: SynthCfg, first_read: int, n: int, bytes_hint: int | None = None) -> DeviceBatch:
         cap = bytes_hint if bytes_hint is not None else n * cfg.max_len
         seq = self.dev_alloc(cap + 64)
@@ -324,8 +339,12 @@ class Ctx:
             self.dev_free(p)
         b.owned = []
 
-    def submit_device(self, b: DeviceBatch, slot: int = 0, max_len_hint: int | None = None):
+    def submit_device(self, b: DeviceBatch, slot: int = 0, max_len_hint: int | None = None, uniform: bool = False):
+        """max_len_hint: None = the batch's own bound, 0 = measure on the device; uniform: every read has exactly
+        that many bases (HPGQ_BATCH_UNIFORM, verified on the device)."""
         hint = b.max_len if max_len_hint is None else max_len_hint
+        if uniform:
+            hint |= BATCH_UNIFORM
         bb = Batch(b.n_reads, hint, b.seq, b.qual, b.idx)
         _ck(self.lib.hpgq_batch_submit_device(self.h, C.byref(bb), C.c_int(slot)), "hpgq_batch_submit_device")
 

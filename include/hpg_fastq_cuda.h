@@ -94,7 +94,7 @@ typedef struct hpgq_params {
 /* SoA batch == fastq_batch_t: read i is bytes [idx[i], idx[i+1]) of seq and of qual. */
 typedef struct hpgq_batch {
   uint32_t n_reads;
-  uint32_t reserved;
+  uint32_t reserved; /* device batches: length hint, see hpgq_batch_submit_device; host batches: ignored */
   const uint8_t *seq;
   const uint8_t *qual;
   const uint32_t *idx; /* n_reads + 1 offsets, idx[0] == 0 for host batches */
@@ -170,6 +170,7 @@ enum hpgq_scalar {
   HPGQ_S_CG_LONG_RUNS,  /* #axis-runs >= 53-12 seen: float/integer CGR may diverge    */
   HPGQ_S_SLOW_READS,    /* reads that took the exact per-byte path (non-ACGTN bytes)  */
   HPGQ_S_BATCHES,
+  HPGQ_S_BAD_BATCH,     /* non-zero: a batch broke the length statement it was submitted with (outputs invalid) */
   HPGQ_S_COUNT = 32
 };
 
@@ -195,7 +196,14 @@ int hpgq_get_layout(hpgq_ctx_t *ctx, hpgq_layout_t *out);
  * cudaMemcpyAsync on the slot's stream and launches the kernels behind the copy. */
 int hpgq_batch_submit(hpgq_ctx_t *ctx, const hpgq_batch_t *host_batch, int slot);
 /* Device-resident batch: pointers are device pointers, 16-byte aligned, each array readable
- * 32 bytes past its logical end; idx need not start at 0.  No copies are made. */
+ * 32 bytes past its logical end; idx need not start at 0.  No copies are made.  The batch's byte span
+ * idx[n] - idx[0] must not exceed hpgq_limits_t.max_bytes_per_batch.
+ * dev_batch->reserved: 0 = the library measures the shortest / longest read on the device first (one stream
+ * synchronisation); L > 0 = the caller states that no read is longer than L (no synchronisation);
+ * L | HPGQ_BATCH_UNIFORM = the caller states that EVERY read has exactly L bases, which selects the
+ * uniform-length kernels.  A statement that turns out false is detected on the device: the batch's outputs are
+ * then invalid and hpgq_batch_wait / hpgq_batch_sync / hpgq_counters_download return HPGQ_ERR_INVALID. */
+#define HPGQ_BATCH_UNIFORM 0x80000000u
 int hpgq_batch_submit_device(hpgq_ctx_t *ctx, const hpgq_batch_t *dev_batch, int slot);
 /* FASTQ text batch: the device-side replacement of the record scan of fastq_fread_se()
  * (reference call sites src/stats_fastq.c:183, src/filter_fastq.c:114, src/edit_fastq.c:121).  `text` is host memory

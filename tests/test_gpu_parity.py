@@ -315,3 +315,137 @@ def test_stats_on_mid_length_reads_register_kernel(q, ob, ooq):
     _, _, _, emask, _ = check(q, ob, q.make_params(q.WORK_STATS | q.WORK_FILTER, filter=flt), seq, qual, idx, 960)
     assert 0 < int(emask.sum()) < len(emask)
     check(q, ob, q.make_params(q.WORK_STATS), seq, qual, idx, 960)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Round 2: the code paths the headline numbers come from.  The in-loop ladder flush (8-bit lanes -> shared u32
+# tables) is reached by a warp only after ~250 of its iterations, i.e. by launches of millions of reads -- or by a
+# small batch when HPGQ_GRID_CAP leaves it two CTAs.  Both kernels (uniform-length aligned-word loop and the general
+# funnel-shift loop, HPGQ_NO_UNI=1) are compared with the oracle word for word.
+class _env:
+    def __init__(self, **kw):
+        self.kw = kw
+
+    def __enter__(self):
+        import os
+        self.old = {k: os.environ.get(k) for k in self.kw}
+        for k, v in self.kw.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = str(v)
+
+    def __exit__(self, *a):
+        import os
+        for k, v in self.old.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+
+
+def _device_check(q, ob, par, seq, qual, idx, Lcap, *, uniform=False, hint=None, lead=0):
+    """Uploads the batch (optionally `lead` junk bytes in front, so that idx[0] != 0), runs it device-resident and
+    compares counters + mask with the oracle."""
+    n = len(idx) - 1
+    if lead:
+        junk = np.full(lead, ord("#"), dtype=np.uint8)
+        seq_d, qual_d = np.concatenate([junk, seq]), np.concatenate([junk, qual])
+        idx_d = (idx.astype(np.uint64) + lead).astype(np.uint32)
+    else:
+        seq_d, qual_d, idx_d = seq, qual, idx
+    with q.Ctx(0, max_reads=max(n, 1), max_bytes=max(int(idx_d[-1]), 16), max_read_len=Lcap, host_staging=False) as ctx:
+        ctx.set_params(par)
+        b = ctx.upload_batch(seq_d, qual_d, idx_d, max_len=int(np.diff(idx).max()) if hint is None else hint)
+        ctx.submit_device(b, 0, uniform=uniform)
+        ctx.sync(0)
+        got = ctx.counters()
+        views = q.Result()
+        q._ck(ctx.lib.hpgq_batch_device_views(ctx.h, 0, __import__("ctypes").byref(views)), "device_views")
+        mask = ctx.dev_download(views.mask, n)
+        lay = ctx.layout
+        ctx.free_batch(b)
+    exp, emask, _ = ob.process_batch(par, lay, seq, qual, idx)
+    assert np.array_equal(mask, emask), f"mask differs at {np.nonzero(mask != emask)[0][:10]}"
+    msg = diff_report(q, lay, got, exp)
+    assert not msg, msg
+    return got
+
+
+C2_FILTER = dict(min_read_length=50, min_read_quality=20, max_N=5)
+
+
+@pytest.mark.parametrize("no_uni", [None, 1])
+def test_bench_shaped_launch_matches_oracle(q, ob, no_uni):
+    """One launch of bench.py's shape: 2^23 x 150 bp, stats + filter, K = 5 / G = 8, all 148 CTAs -- every consumer
+    warp runs ~470 iterations, past the in-loop flush at 248.  Whole counter block and mask against the oracle."""
+    n = 1 << 23
+    cfg = q.synth_cfg(150)
+    par = q.make_params(q.WORK_STATS | q.WORK_FILTER, filter=C2_FILTER)
+    with _env(HPGQ_NO_UNI=no_uni), q.Ctx(0, max_reads=n, max_bytes=n * 150, max_read_len=160, host_staging=False) as ctx:
+        ctx.set_params(par)
+        b = ctx.synth_device(cfg, 0, n)
+        ctx.submit_device(b, 0, uniform=True)
+        ctx.sync(0)
+        got = ctx.counters()
+        views = q.Result()
+        q._ck(ctx.lib.hpgq_batch_device_views(ctx.h, 0, __import__("ctypes").byref(views)), "device_views")
+        mask = ctx.dev_download(views.mask, n)
+        seq = ctx.dev_download(b.seq, b.n_bytes)
+        qual = ctx.dev_download(b.qual, b.n_bytes)
+        idx = ctx.dev_download(b.idx, (n + 1) * 4).view(np.uint32)
+        lay = ctx.layout
+        ctx.free_batch(b)
+    exp, emask, _ = ob.process_batch(par, lay, seq, qual, idx)
+    assert np.array_equal(mask, emask)
+    msg = diff_report(q, lay, got, exp)
+    assert not msg, msg
+    assert int(got[q.S["NUM_PASSED"]]) + int(got[q.S["NUM_FAILED"]]) == n
+
+
+@pytest.mark.parametrize("no_uni", [None, 1])
+@pytest.mark.parametrize("L,n", [(76, 70000), (150, 36000), (300, 18000), (600, 9500), (36, 140000)])
+def test_in_loop_flush_every_geometry(q, ob, L, n, no_uni):
+    """Two CTAs (HPGQ_GRID_CAP): each consumer warp passes iteration 255 of every ladder cadence
+    (G = 4, 8, 16, 32: MERGED and !MERGED), uniform reads and a ragged variant."""
+    par = q.make_params(q.WORK_STATS | q.WORK_FILTER, filter=dict(min_read_length=min(50, L), min_read_quality=20, max_N=5))
+    with _env(HPGQ_NO_UNI=no_uni, HPGQ_GRID_CAP=2):
+        seq, qual, idx = q.synth_host(q.synth_cfg(L), 0, n)
+        _device_check(q, ob, par, seq, qual, idx, 640, uniform=True)
+        if no_uni:
+            seq, qual, idx = q.synth_host(q.synth_cfg(L, short_pct=3, short_min=min(35, L // 2)), 0, n)
+            _device_check(q, ob, par, seq, qual, idx, 640)
+
+
+@pytest.mark.parametrize("L", [7, 36, 75, 100, 101, 149, 150, 151, 250, 251, 253, 300, 301, 302, 600, 637, 640])
+def test_uniform_kernel_lengths_and_phases(q, ob, L):
+    """Uniform-length kernel over the geometries' length range, odd lengths (where the group count does not keep the
+    byte phase the kernel must not be chosen) and every start phase idx[0] mod 4 / mod 16."""
+    n = 9000
+    seq, qual, idx = q.synth_host(q.synth_cfg(L, lowercase_ppm=300), 0, n)
+    par = q.make_params(q.WORK_STATS | q.WORK_FILTER, filter=dict(min_read_length=5, min_read_quality=20, max_N=5))
+    for lead in (0, 1, 2, 3, 13):
+        _device_check(q, ob, par, seq, qual, idx, 640, uniform=True, lead=lead)
+    full = dict(min_read_length=5, min_read_quality=22, max_read_quality=39, max_out_of_quality=L // 3 + 2,
+                left_length=10, min_left_quality=30, max_left_quality=41, right_length=12, min_right_quality=15,
+                max_right_quality=40, max_N=3)
+    par = q.make_params(q.WORK_STATS | q.WORK_FILTER, filter=full)
+    for lead in (0, 7):
+        _device_check(q, ob, par, seq, qual, idx, 640, uniform=True, lead=lead)
+    _device_check(q, ob, q.make_params(q.WORK_STATS), seq, qual, idx, 640, uniform=True, lead=2)
+
+
+def test_false_length_statements_fail_loudly(q, ob):
+    """hpgq_batch_t.reserved: a uniform-length claim or a max-length bound that the batch breaks is detected on the
+    device and reported by hpgq_batch_sync / hpgq_counters_download, never silently wrong."""
+    par = q.make_params(q.WORK_STATS | q.WORK_FILTER, filter=C2_FILTER)
+    seq, qual, idx = q.synth_host(q.synth_cfg(150, short_pct=2), 0, 50000)
+    assert int(np.diff(idx).min()) < 150
+    with pytest.raises(q.HpgqError, match="length statement"):
+        _device_check(q, ob, par, seq, qual, idx, 160, uniform=True, hint=150)
+    seq, qual, idx = q.synth_host(q.synth_cfg((100, 600)), 0, 50000)
+    with pytest.raises(q.HpgqError, match="length statement"):
+        _device_check(q, ob, par, seq, qual, idx, 640, hint=120)
+    # the same batches with true statements
+    _device_check(q, ob, par, seq, qual, idx, 640, hint=600)
+    _device_check(q, ob, par, seq, qual, idx, 640, hint=0)
