@@ -7,6 +7,7 @@
 // add) -> warp-per-read copy of seq and qual bytes to their final offsets.
 #include "hpgq_dev.cuh"
 #include "hpgq_internal.h"
+#include "../../include/hpgq_synth.h"
 
 namespace {
 
@@ -379,7 +380,36 @@ __global__ void __launch_bounds__(256) hq_compact_copy_tile(hq_kargs a, hq_compa
   if (blockIdx.x == 0 && tid == 0) b.out_idx[n] = tot.x + tot.y;
 }
 
+// Order-sensitive 64-bit checksum of a slot's compacted output (bench.py compares it across GPU counts, tests with
+// the host twin hpgq_checksum_host): sum over every output byte / offset / source index of mix(position, value).
+__device__ __forceinline__ unsigned long long ck_mix(unsigned long long pos, unsigned long long v) {
+  return hpgq_checksum_mix(pos, v);
+}
+__global__ void hq_checksum_kernel(hq_compact_bufs b, uint32_t n, unsigned long long *out) {
+  const uint32_t T = b.totals[2] + b.totals[3];
+  unsigned long long h = 0;
+  const uint32_t stride = gridDim.x * blockDim.x, t0 = blockIdx.x * blockDim.x + threadIdx.x;
+  for (uint32_t i = t0; i < T; i += stride) {
+    h += ck_mix(i, b.out_seq[i]);
+    h += ck_mix((unsigned long long)T + i, b.out_qual[i]);
+  }
+  for (uint32_t j = t0; j <= n; j += stride) h += ck_mix(2ull * T + j, b.out_idx[j]);
+  for (uint32_t j = t0; j < n; j += stride) h += ck_mix(2ull * T + n + 1ull + j, b.out_src[j]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) h += __shfl_xor_sync(0xFFFFFFFFu, h, o);
+  if ((threadIdx.x & 31u) == 0 && h) atomicAdd(out, h);
+}
+
 } // namespace
+
+cudaError_t hq_launch_checksum(const hq_compact_bufs &b, uint32_t n, unsigned long long *d_out, cudaStream_t st,
+                               uint64_t *launches) {
+  cudaError_t e = cudaMemsetAsync(d_out, 0, 8, st);
+  if (e != cudaSuccess) return e;
+  hq_checksum_kernel<<<148 * 8, 256, 0, st>>>(b, n, d_out);
+  ++*launches;
+  return cudaGetLastError();
+}
 
 cudaError_t hq_launch_compact(const hq_kargs &a, const hq_compact_bufs &b, uint32_t mean_len, uint32_t max_len,
                               cudaStream_t st, uint64_t *launches) {

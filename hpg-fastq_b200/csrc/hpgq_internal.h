@@ -68,6 +68,9 @@ struct hq_compact_bufs {
 cudaError_t hq_launch_compact(const hq_kargs &a, const hq_compact_bufs &b, uint32_t mean_len, uint32_t max_len,
                               cudaStream_t st, uint64_t *launches);
 
+cudaError_t hq_launch_checksum(const hq_compact_bufs &b, uint32_t n, unsigned long long *d_out, cudaStream_t st,
+                               uint64_t *launches);
+
 cudaError_t hq_launch_synth(const hpgq_synth_cfg_t &cfg, uint64_t first_read, uint32_t n, uint8_t *d_seq,
                             uint8_t *d_qual, const uint32_t *d_idx, cudaStream_t st, uint64_t *launches);
 

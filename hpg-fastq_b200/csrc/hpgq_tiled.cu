@@ -62,7 +62,8 @@ bool pick_geom(uint32_t max_len, bool uniform, uint32_t n_reads, int sm_count, s
   // reads per tile: a multiple of lcm(NGB, 4) that fits the per-stage budget
   uint32_t unit = NGB;
   while (unit % 4u) unit += NGB;
-  const size_t budget = (smem_limit - SM_STAGES) / NS;
+  const uint32_t sm_front = sm_carve(4u * bK * bG).stages;  // tables of this geometry, then the ring
+  const size_t budget = (smem_limit - sm_front) / NS;
   uint32_t RT = 0;
   for (uint32_t cand = unit; cand <= 65535u - unit; cand += unit) {
     const size_t need = idx_cap_bytes(cand) + 2ull * ((((size_t)cand * max_len + 48u + pad) + 127u) & ~127ull);
@@ -84,7 +85,7 @@ bool pick_geom(uint32_t max_len, bool uniform, uint32_t n_reads, int sm_count, s
   out->RT = RT;
   out->NS = NS;
   out->stage_bytes = (uint32_t)((((size_t)RT * max_len + 48u + pad) + 127u) & ~127ull);
-  out->smem_bytes = SM_STAGES + NS * (idx_cap_bytes(RT) + 2u * out->stage_bytes);
+  out->smem_bytes = sm_front + NS * (idx_cap_bytes(RT) + 2u * out->stage_bytes);
   return true;
 }
 

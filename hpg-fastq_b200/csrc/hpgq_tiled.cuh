@@ -37,21 +37,26 @@ constexpr int NSMAX = 8;                 // pipeline stages are a launch paramet
 #endif
 constexpr int NCW = HQ_NCW;              // consumer warps (+ producer = 4 warps per SM sub-partition: 128 registers each)
 constexpr int THREADS = (NCW + 1) * 32;
-constexpr int TAB = 640;                 // positions held by the block-private tables
 constexpr int KMAX = 5;
 
-// fixed shared-memory carve-up (bytes)
-constexpr uint32_t SM_BAR = 0;                               // full[NSMAX], empty[NSMAX] (u64)
-constexpr uint32_t SM_TAB = 256;                             // u32 [6][TAB]: accq, A, C, G, T, other
-constexpr uint32_t SM_LEN = SM_TAB + 4u * 6u * TAB;          // u32 [TAB + 4]
-constexpr uint32_t SM_QH = SM_LEN + 4u * (TAB + 4);          // u32 [256]
-constexpr uint32_t SM_GC = SM_QH + 4u * 256u;                // u32 [104]
-constexpr uint32_t SM_SUMQ = SM_GC + 4u * 104u;              // u64 [TAB + 4]
-constexpr uint32_t SM_CNT = SM_SUMQ + 8u * (TAB + 4);        // u32 [TAB + 4]: reads covering position j
-constexpr uint32_t SM_RECS = SM_CNT + 4u * (TAB + 4);        // uint4 [NCW][32]
-constexpr uint32_t SM_STAGES = (SM_RECS + 16u * NCW * 32u + 127u) & ~127u;
-static_assert(SM_SUMQ % 8 == 0, "sumq must be 8-byte aligned");
-static_assert(SM_RECS % 16 == 0, "records must be 16-byte aligned");
+// Shared-memory carve-up (bytes) in front of the ring, sized by the frame of the geometry: POS = 4 K G positions
+// (160 for 150 bp reads, at most 640), so that short-read geometries leave more room for ring stages.
+struct sm_layout {
+  uint32_t tab, len, qh, gc, sumq, cnt, recs, stages;
+};
+__host__ __device__ constexpr sm_layout sm_carve(uint32_t POS) {
+  sm_layout l{};
+  l.tab = 256;                               // [0, 256): full[NSMAX], empty[NSMAX] (u64)
+  l.len = l.tab + 4u * 6u * POS;             // u32 [6][POS]: accq, A, C, G, T, other
+  l.qh = l.len + 4u * (POS + 4u);            // u32 [POS + 4]: reads of each length
+  l.gc = l.qh + 4u * 256u;                   // u32 [256]
+  l.sumq = (l.gc + 4u * 104u + 7u) & ~7u;    // u32 [104]; then u64 [POS + 4]: sum of quality by length
+  l.cnt = l.sumq + 8u * (POS + 4u);          // u32 [POS + 4]: reads covering position j
+  l.recs = (l.cnt + 4u * (POS + 4u) + 15u) & ~15u;  // uint4 [NCW][32]
+  l.stages = (l.recs + 16u * NCW * 32u + 127u) & ~127u;
+  return l;
+}
+constexpr uint32_t SM_BAR = 0;
 
 __host__ __device__ inline uint32_t idx_cap_bytes(uint32_t RT) { return (((RT + 1u) * 4u + 15u) & ~15u) + 16u; }
 

@@ -104,7 +104,7 @@ EXPORTS = [
     "hpgq_strerror", "hpgq_last_error", "hpgq_layout", "hpgq_device_count", "hpgq_ctx_create", "hpgq_ctx_destroy",
     "hpgq_set_params", "hpgq_get_layout", "hpgq_batch_submit", "hpgq_batch_submit_device", "hpgq_batch_wait",
     "hpgq_batch_submit_text", "hpgq_batch_text_headers", "hpgq_batch_wait_text",
-    "hpgq_batch_sync", "hpgq_batch_device_views", "hpgq_counters_reset", "hpgq_counters_download",
+    "hpgq_batch_sync", "hpgq_batch_device_views", "hpgq_batch_checksum", "hpgq_checksum_host", "hpgq_counters_reset", "hpgq_counters_download",
     "hpgq_counters_device_ptr", "hpgq_counters_reduce", "hpgq_counters_finalize_host", "hpgq_slot_stream", "hpgq_launch_count",
     "hpgq_last_kernel_ms", "hpgq_synth_device", "hpgq_synth_host", "hpgq_dev_alloc", "hpgq_dev_free",
     "hpgq_dev_download", "hpgq_dev_upload", "hpgq_host_alloc_pinned", "hpgq_host_free_pinned", "hpgq_version",
@@ -351,6 +351,12 @@ class Ctx:
     def sync(self, slot: int = 0):
         _ck(self.lib.hpgq_batch_sync(self.h, C.c_int(slot)), "hpgq_batch_sync")
 
+    def checksum(self, slot: int = 0) -> int:
+        """Order-sensitive 64-bit checksum of the slot's compacted output (hpgq_batch_checksum)."""
+        out = C.c_uint64(0)
+        _ck(self.lib.hpgq_batch_checksum(self.h, C.c_int(slot), C.byref(out)), "hpgq_batch_checksum")
+        return out.value
+
     def last_kernel_ms(self, slot: int = 0) -> float:
         ms = C.c_float(0)
         _ck(self.lib.hpgq_last_kernel_ms(self.h, C.c_int(slot), C.byref(ms)), "hpgq_last_kernel_ms")
@@ -381,6 +387,14 @@ class Ctx:
         p = C.c_void_p()
         _ck(self.lib.hpgq_slot_stream(self.h, C.c_int(slot), C.byref(p)), "hpgq_slot_stream")
         return p.value or 0
+
+
+def checksum_host(out_seq: np.ndarray, out_qual: np.ndarray, out_idx: np.ndarray, out_src: np.ndarray) -> int:
+    lib = load_library()
+    lib.hpgq_checksum_host.restype = C.c_uint64
+    n = len(out_src)
+    a = [np.ascontiguousarray(x) for x in (out_seq, out_qual, out_idx.astype(np.uint32), out_src.astype(np.uint32))]
+    return int(lib.hpgq_checksum_host(*[x.ctypes.data_as(C.c_void_p) for x in a], C.c_uint32(n), C.c_uint64(len(out_seq))))
 
 
 def finalize_host(lay: Layout, block: np.ndarray):

@@ -245,6 +245,15 @@ int hpgq_batch_sync(hpgq_ctx_t *ctx, int slot);
 /* device views of the slot's outputs (mask / trim / compacted arrays), valid until resubmit */
 int hpgq_batch_device_views(hpgq_ctx_t *ctx, int slot, hpgq_batch_result_t *res);
 
+/* Order-sensitive 64-bit checksum of the compacted output (HPGQ_WORK_COMPACT) a slot holds, computed on the
+ * device; the slot must be idle (after hpgq_batch_wait / hpgq_batch_sync).  hpgq_checksum_host is the same sum over
+ * host arrays: sum of hpgq_checksum_mix(position, value) (include/hpgq_synth.h) over out_seq[0..T), out_qual[0..T) (positions T + i),
+ * out_idx[0..n] (2T + j) and out_src[0..n) (2T + n + 1 + j), T = passed + failed bytes.  Measurement / test aid
+ * (SURVEY.md 8d "64-bit order-sensitive checksums"); replaces nothing in the reference. */
+int hpgq_batch_checksum(hpgq_ctx_t *ctx, int slot, uint64_t *out);
+uint64_t hpgq_checksum_host(const uint8_t *out_seq, const uint8_t *out_qual, const uint32_t *out_idx,
+                            const uint32_t *out_src, uint32_t n_reads, uint64_t total_bytes);
+
 int hpgq_counters_reset(hpgq_ctx_t *ctx);
 /* Copies the flat counter block (layout words) to host memory and fills the derived scalars. */
 int hpgq_counters_download(hpgq_ctx_t *ctx, uint64_t *dst, size_t n_words);
@@ -301,4 +310,5 @@ const char *hpgq_version(void);
 #ifdef __cplusplus
 }
 #endif
+
 #endif /* HPG_FASTQ_CUDA_H */

@@ -98,4 +98,15 @@ HPGQ_HD void hpgq_synth_read_fill(const hpgq_synth_cfg_t *cfg, uint64_t read_ind
   }
 }
 
+/* splitmix64 finaliser of (position, value); shared by the device kernel and hpgq_checksum_host */
+#if defined(__CUDACC__)
+__host__ __device__
+#endif
+static inline unsigned long long hpgq_checksum_mix(unsigned long long pos, unsigned long long v) {
+  unsigned long long z = pos * 0x9E3779B97F4A7C15ull + (v + 1ull) * 0xD1B54A32D192ED03ull;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  return z ^ (z >> 31);
+}
+
 #endif /* HPGQ_SYNTH_H */
