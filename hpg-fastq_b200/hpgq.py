@@ -351,11 +351,11 @@ class Ctx:
     def sync(self, slot: int = 0):
         _ck(self.lib.hpgq_batch_sync(self.h, C.c_int(slot)), "hpgq_batch_sync")
 
-    def checksum(self, slot: int = 0) -> int:
-        """Order-sensitive 64-bit checksum of the slot's compacted output (hpgq_batch_checksum)."""
-        out = C.c_uint64(0)
-        _ck(self.lib.hpgq_batch_checksum(self.h, C.c_int(slot), C.byref(out)), "hpgq_batch_checksum")
-        return out.value
+    def checksum(self, slot: int = 0) -> dict:
+        """hpgq_batch_checksum: order-sensitive 64-bit checksum of the slot's compacted output + its sizes."""
+        out = (C.c_uint64 * 4)()
+        _ck(self.lib.hpgq_batch_checksum(self.h, C.c_int(slot), out), "hpgq_batch_checksum")
+        return dict(checksum=int(out[0]), passed_bytes=int(out[1]), failed_bytes=int(out[2]), n_passed=int(out[3]))
 
     def last_kernel_ms(self, slot: int = 0) -> float:
         ms = C.c_float(0)

@@ -250,7 +250,7 @@ int hpgq_batch_device_views(hpgq_ctx_t *ctx, int slot, hpgq_batch_result_t *res)
  * host arrays: sum of hpgq_checksum_mix(position, value) (include/hpgq_synth.h) over out_seq[0..T), out_qual[0..T) (positions T + i),
  * out_idx[0..n] (2T + j) and out_src[0..n) (2T + n + 1 + j), T = passed + failed bytes.  Measurement / test aid
  * (SURVEY.md 8d "64-bit order-sensitive checksums"); replaces nothing in the reference. */
-int hpgq_batch_checksum(hpgq_ctx_t *ctx, int slot, uint64_t *out);
+int hpgq_batch_checksum(hpgq_ctx_t *ctx, int slot, uint64_t out[4]); /* checksum, passed bytes, failed bytes, passed reads */
 uint64_t hpgq_checksum_host(const uint8_t *out_seq, const uint8_t *out_qual, const uint32_t *out_idx,
                             const uint32_t *out_src, uint32_t n_reads, uint64_t total_bytes);
 

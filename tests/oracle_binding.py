@@ -136,5 +136,16 @@ def chaos_reference(seq, qual, idx, k, base_quality=33):
     return ts, tq, words.value
 
 
+def merge_hash_faithful(lay, seq, qual, idx):
+    """oracle_merge_hash_faithful: the reference consumer's per-base hash insertions (src/stats_fastq.c:338-382)."""
+    n = len(idx) - 1
+    counters = np.zeros(int(lay.offset[len(lay.offset) - 1]), dtype=np.uint64)
+    rc = lib().oracle_merge_hash_faithful(C.byref(lay), C.c_uint32(n), _p(np.ascontiguousarray(seq)),
+                                          _p(np.ascontiguousarray(qual)), _p(np.ascontiguousarray(idx, dtype=np.uint32)),
+                                          _p(counters))
+    assert rc == 0
+    return counters
+
+
 def max_threads():
     return lib().oracle_max_threads()

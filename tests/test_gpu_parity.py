@@ -449,3 +449,25 @@ def test_false_length_statements_fail_loudly(q, ob):
     # the same batches with true statements
     _device_check(q, ob, par, seq, qual, idx, 640, hint=600)
     _device_check(q, ob, par, seq, qual, idx, 640, hint=0)
+
+
+def test_compaction_checksum_matches_host_twin(q, ob):
+    """hpgq_batch_checksum (device) == hpgq_checksum_host over the oracle's compacted arrays; order-sensitive."""
+    seq, qual, idx = q.synth_host(q.synth_cfg(150, short_pct=3), 0, 40000)
+    par = q.make_params(q.WORK_EDIT | q.WORK_FILTER | q.WORK_COMPACT, filter=C2_FILTER,
+                        edit=dict(left_length=10, min_left_quality=20, right_length=10, min_right_quality=20))
+    with q.Ctx(0, max_reads=40000, max_bytes=int(idx[-1]), max_read_len=160) as ctx:
+        ctx.set_params(par)
+        ctx.submit(seq, qual, idx, 0)
+        res = ctx.wait(0)
+        ck = ctx.checksum(0)
+        lay = ctx.layout
+    exp, emask, etrim = ob.process_batch(par, lay, seq, qual, idx)
+    cp = ob.compact(seq, qual, idx, emask, etrim)
+    assert ck["passed_bytes"] == cp["passed_bytes"] and ck["failed_bytes"] == cp["failed_bytes"]
+    assert ck["n_passed"] == cp["n_passed"]
+    assert ck["checksum"] == q.checksum_host(cp["out_seq"], cp["out_qual"], cp["out_idx"], cp["out_src"])
+    swapped = cp["out_seq"].copy()
+    swapped[[0, 1]] = swapped[[1, 0]]
+    if swapped[0] != swapped[1]:
+        assert ck["checksum"] != q.checksum_host(swapped, cp["out_qual"], cp["out_idx"], cp["out_src"])
