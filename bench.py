@@ -252,7 +252,7 @@ def emit(line):
     out.flush()
 
 
-IGNORED_SCALARS = ("SLOW_READS", "BATCHES", "CG_LONG_RUNS")
+IGNORED_SCALARS = ("SLOW_READS", "BATCHES", "CG_LONG_RUNS", "CG_FIXED_READS", "CG_MOVED_WORDS")
 
 
 def verify_against_oracle(q, ob, ctx, par, batches, want_reads, threads):

@@ -50,6 +50,7 @@ struct hpgq_slot {
   const uint32_t *c_idx = nullptr;
   // outputs
   uint8_t *d_mask = nullptr, *h_mask = nullptr;
+  uint8_t *d_cgflag = nullptr;  // chaos game: reads to re-emulate in double arithmetic
   hpgq_trim_t *d_trim = nullptr, *h_trim = nullptr;
   uint32_t *d_maxlen = nullptr, *h_small = nullptr; // h_small: [0..2]=max/min length, order flag [4..7]=totals [8..9]=HPGQ_S_BAD_BATCH (pinned)
   hq_compact_bufs cb = {};
@@ -176,6 +177,7 @@ static void slot_free(hpgq_slot &s) {
   cudaFree(s.d_seq); cudaFree(s.d_qual); cudaFree(s.d_idx);
   cudaFreeHost(s.h_seq); cudaFreeHost(s.h_qual); cudaFreeHost(s.h_idx);
   cudaFree(s.d_mask); cudaFreeHost(s.h_mask);
+  cudaFree(s.d_cgflag);
   cudaFree(s.d_trim); cudaFreeHost(s.h_trim);
   cudaFree(s.d_maxlen); cudaFreeHost(s.h_small);
   cudaFree(s.cb.scan); cudaFree(s.cb.block_sums); cudaFree(s.cb.out_seq); cudaFree(s.cb.out_qual);
@@ -244,6 +246,7 @@ extern "C" int hpgq_ctx_create(int device, const hpgq_limits_t *lim, hpgq_ctx_t 
     if (e == cudaSuccess) e = cudaMalloc(&s.d_maxlen, 64);
     if (e == cudaSuccess) e = cudaMallocHost(&s.h_small, 64);
     if (e == cudaSuccess) e = cudaMalloc(&s.d_mask, nr + 64);
+    if (e == cudaSuccess && lim->cg_k) e = cudaMalloc(&s.d_cgflag, nr + 64);
     if (lim->host_staging) {
       if (e == cudaSuccess) e = cudaMalloc(&s.d_seq, nb);
       if (e == cudaSuccess) e = cudaMalloc(&s.d_qual, nb);

@@ -32,6 +32,7 @@ struct hq_kargs {
   // per-read outputs
   uint8_t *mask;     // may be NULL
   hpgq_trim_t *trim; // may be NULL
+  uint8_t *cgflag;   // chaos game: reads to re-emulate in double arithmetic (n_reads bytes), may be NULL
   // tiled-kernel geometry
   uint32_t RT;          // reads per tile (multiple of 4)
   uint32_t G;           // lanes per read group

@@ -197,7 +197,12 @@ __global__ void __launch_bounds__(256) hq_kmers_cg_kernel(hq_kargs a) {
     other = (__ballot_sync(0xFFFFFFFFu, other) & gmask) != 0u;
     single_x = (__ballot_sync(0xFFFFFFFFu, single_x) & gmask) == gmask;
     single_y = (__ballot_sync(0xFFFFFFFFu, single_y) & gmask) == gmask;
-    if (do_cg && lig == 0 && L != 0u && (single_x || single_y)) longruns++;
+    // reads that may take the reference's double arithmetic off the integer form (hq_cg_fix_kernel re-emulates them):
+    // an axis run of >= 21 bases inside the read, or a read that lies on one axis throughout (runs span reads)
+    if (do_cg && lig == 0 && L != 0u && (single_x || single_y)) {
+      longruns++;
+      if (a.cgflag) a.cgflag[r] = 1;
+    }
 
     const uint32_t chunk = (L + (uint32_t)G - 1u) / (uint32_t)G;
     const uint32_t cb = lig * chunk, ce = min(L, cb + chunk);
@@ -241,7 +246,10 @@ __global__ void __launch_bounds__(256) hq_kmers_cg_kernel(hq_kargs a) {
               cg_add(a, ((uint64_t)ix << ck) + iy, accq - (uint32_t)(a.cg_base_quality * ck));
               words++;
             }
-            if (run_x == 21u || run_y == 21u) longruns++;
+            if (run_x == 21u || run_y == 21u) {
+              longruns++;
+              if (a.cgflag) a.cgflag[r] = 1;
+            }
           }
         }
       }
@@ -259,7 +267,10 @@ __global__ void __launch_bounds__(256) hq_kmers_cg_kernel(hq_kargs a) {
           iy = (iy >> 1) | (yb << (ck - 1));
           run_x = xb ? run_x + 1 : 0;
           run_y = yb ? run_y + 1 : 0;
-          if (run_x == 21u || run_y == 21u) longruns++;
+          if (run_x == 21u || run_y == 21u) {
+            longruns++;
+            if (a.cgflag) a.cgflag[r] = 1;
+          }
           cnt++;
           accq += (uint32_t)(int32_t)(signed char)q[j];
         } else if (c == 'N') {
@@ -289,6 +300,110 @@ __global__ void __launch_bounds__(256) hq_kmers_cg_kernel(hq_kargs a) {
     if (words) atomicAdd(&C[HPGQ_S_CG_WORDS], words);
     if (longruns) atomicAdd(&C[HPGQ_S_CG_LONG_RUNS], longruns);
   }
+}
+
+// ---------------------------------------------------------------- chaos game: exact double arithmetic where it matters
+// The reference carries (f_x, f_y) as doubles across all reads of a batch (old/chaos_game.c:180-181,200-251).  Its
+// cell index equals the integer form used above except after an axis run of >= 53 - k bases, where the rounding of
+// f + (dim - f) * 0.5 carries through the run (SURVEY.md Appendix C probe 1), and where f reaches dim exactly while
+// no word completes (the EPSILON clamp of :243-251 is only applied at word completions).  One thread per FLAGGED read
+// re-runs the reference loop literally: it warms the double state up over the >= 128 bases in front of the read from
+// the two extreme states 0 and dim -- the trajectories contract by half per base and must have met bit for bit at
+// the read's first base, else the warm-up is lengthened, down to the batch start where the state is dim / 2 exactly --
+// then walks the read (and the unflagged reads behind it while a run's tail is still within k + 1 bases) with the
+// double and the integer index side by side and moves every word whose cells differ.
+__device__ __forceinline__ double cg_up(double f, double dim) { return __dadd_rn(f, __dmul_rn(__dsub_rn(dim, f), 0.5)); }
+
+__global__ void __launch_bounds__(128) hq_cg_fix_kernel(hq_kargs a, const uint8_t *flag) {
+  const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= a.n_reads || !flag[r]) return;
+  const int k = a.cg_k, dim = 1 << k;
+  const double dimd = (double)dim, EPS = 0.00001;  // old/chaos_game.h:41
+  const uint32_t qsub = (uint32_t)(a.cg_base_quality * k);
+  unsigned long long *C = a.ctr;
+  uint32_t patched = 0;
+  for (uint32_t W = 128u;; W = W >= (1u << 24) ? 0xFFFFFFFFu : W * 8u) {
+    uint32_t rs = r, have = 0;
+    while (rs > 0u && have < W) {
+      --rs;
+      have += a.idx[rs + 1] - a.idx[rs];
+    }
+    const bool exact = rs == 0u;  // batch start: f = dim / 2 (old/chaos_game.c:107-108 via :180-181)
+    double fx[2], fy[2];
+    fx[0] = fy[0] = exact ? dimd * 0.5 : 0.0;
+    fx[1] = fy[1] = exact ? dimd * 0.5 : dimd;
+    uint32_t ix = 0, iy = 0, acc = 0, run_x = 0, run_y = 0, since = 0xFFFFu;
+    int cnt = 0;
+    bool patching = false, redo = false;
+    for (uint32_t i = rs; i < a.n_reads; ++i) {
+      if (i == r) {
+        if (fx[0] != fx[1] || fy[0] != fy[1]) {
+          redo = true;  // the two warm-up trajectories have not met yet: start further upstream
+          break;
+        }
+        patching = true;
+      } else if (i > r && (flag[i] || since > (uint32_t)k + 1u)) {
+        break;  // the next flagged read has its own thread; or no run's tail reaches into this read
+      }
+      const uint32_t o = a.idx[i], L = a.idx[i + 1] - o;
+      for (uint32_t j = 0; j < L; ++j) {
+        const uint32_t c = a.seq[o + j];
+        const int b = base2(c);
+        if (b >= 0) {
+          const uint32_t xb = (b == 0 || b == 3), yb = (b == 2 || b == 3);
+#pragma unroll
+          for (int t = 0; t < 2; ++t) {
+            fx[t] = xb ? cg_up(fx[t], dimd) : __dmul_rn(fx[t], 0.5);
+            fy[t] = yb ? cg_up(fy[t], dimd) : __dmul_rn(fy[t], 0.5);
+          }
+          ix = (ix >> 1) | (xb << (k - 1));
+          iy = (iy >> 1) | (yb << (k - 1));
+          run_x = xb ? run_x + 1u : 0u;
+          run_y = yb ? run_y + 1u : 0u;
+          since = (run_x >= 21u || run_y >= 21u) ? 0u : min(since + 1u, 0xFFFFu);
+          cnt++;
+          acc += (uint32_t)(int32_t)(signed char)a.qual[o + j];
+        } else if (c == 'N') {
+          cnt = 0;
+          acc = 0;
+        }
+        if (cnt == k) {
+          int cx[2], cy[2];
+#pragma unroll
+          for (int t = 0; t < 2; ++t) {
+            cx[t] = __double2int_rz(fx[t]);
+            cy[t] = __double2int_rz(fy[t]);
+            if (cx[t] == dim) {
+              cx[t] = dim - 1;
+              fx[t] = __dsub_rn(fx[t], EPS);
+            }
+            if (cy[t] == dim) {
+              cy[t] = dim - 1;
+              fy[t] = __dsub_rn(fy[t], EPS);
+            }
+          }
+          if (patching) {
+            const uint64_t cd = ((uint64_t)cx[0] << k) + (uint32_t)cy[0], ci = ((uint64_t)ix << k) + iy;
+            if (cd != ci) {
+              const unsigned long long qv = (unsigned long long)(uint32_t)(acc - qsub);
+              atomicAdd(&C[a.o_cg_seq + ci], ~0ull);
+              atomicAdd(&C[a.o_cg_seq + cd], 1ull);
+              atomicAdd(&C[a.o_cg_q + ci], 0ull - qv);
+              atomicAdd(&C[a.o_cg_q + cd], qv);
+              patched++;
+            }
+          }
+          cnt--;
+          acc -= (uint32_t)(int32_t)(signed char)a.qual[o + j + 1u - (uint32_t)k];
+        }
+      }
+      cnt = 0;
+      acc = 0;
+    }
+    if (!redo) break;
+  }
+  atomicAdd(&C[HPGQ_S_CG_FIXED_READS], 1ull);
+  if (patched) atomicAdd(&C[HPGQ_S_CG_MOVED_WORDS], (unsigned long long)patched);
 }
 
 // ---------------------------------------------------------------- 5-mer x start-position table
@@ -488,11 +603,16 @@ cudaError_t hq_launch_kmers_cg(const hq_kargs &a0, uint32_t max_len_in_batch, cu
     ++*launches;
   }
   if (!(a0.work & HPGQ_WORK_CHAOS) && !((a0.work & HPGQ_WORK_KMERS) && a0.k2 > 0)) return cudaGetLastError();
+  if (cg && a0.cgflag) {
+    cudaError_t e = cudaMemsetAsync(a0.cgflag, 0, a0.n_reads, st);
+    if (e != cudaSuccess) return e;
+  }
   for (uint32_t first = 0; first < a0.n_reads; first += chunk) {
     hq_kargs a = a0;
     a.n_reads = a0.n_reads - first < chunk ? a0.n_reads - first : chunk;
     a.idx = a0.idx + first;
     if (a.mask) a.mask = a0.mask + first;
+    if (a.cgflag) a.cgflag = a0.cgflag + first;
     const bool narrow = max_len_in_batch <= 1024u;
     uint32_t blocks = (a.n_reads + (narrow ? 63u : 7u)) / (narrow ? 64u : 8u);
     if (blocks > 148u * 16u) blocks = 148u * 16u;
@@ -504,6 +624,10 @@ cudaError_t hq_launch_kmers_cg(const hq_kargs &a0, uint32_t max_len_in_batch, cu
       hq_cg_unpack_kernel<<<(cells + 1023u) / 1024u < 592u ? (cells + 1023u) / 1024u : 592u, 256, 0, st>>>(a, cells);
       ++*launches;
     }
+  }
+  if (cg && a0.cgflag) {
+    hq_cg_fix_kernel<<<(a0.n_reads + 127u) / 128u, 128, 0, st>>>(a0, a0.cgflag);
+    ++*launches;
   }
   return cudaGetLastError();
 }

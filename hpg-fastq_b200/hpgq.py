@@ -28,6 +28,7 @@ SEC_COUNT = len(SEC_NAMES)
 SCALAR_NAMES = [
     "NUM_READS", "NUM_PASSED", "NUM_FAILED", "NUM_EDITED", "ACC_LENGTH", "NUM_A", "NUM_C", "NUM_G", "NUM_T",
     "NUM_N", "MIN_LENGTH", "MAX_LENGTH", "CG_WORDS", "CG_LONG_RUNS", "SLOW_READS", "BATCHES", "BAD_BATCH",
+    "CG_FIXED_READS", "CG_MOVED_WORDS",
 ]
 BATCH_UNIFORM = 0x80000000
 S = {n: i for i, n in enumerate(SCALAR_NAMES)}

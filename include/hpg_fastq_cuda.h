@@ -167,10 +167,12 @@ enum hpgq_scalar {
   HPGQ_S_MIN_LENGTH, /* derived at download from LEN_HIST (100000 if no reads: src/stats_fastq.c:24) */
   HPGQ_S_MAX_LENGTH,
   HPGQ_S_CG_WORDS,      /* fq_word_count                                             */
-  HPGQ_S_CG_LONG_RUNS,  /* #axis-runs >= 53-12 seen: float/integer CGR may diverge    */
+  HPGQ_S_CG_LONG_RUNS,  /* informational: axis runs >= 21 bases / single-axis reads seen (re-emulated exactly) */
   HPGQ_S_SLOW_READS,    /* reads that took the exact per-byte path (non-ACGTN bytes)  */
   HPGQ_S_BATCHES,
   HPGQ_S_BAD_BATCH,     /* non-zero: a batch broke the length statement it was submitted with (outputs invalid) */
+  HPGQ_S_CG_FIXED_READS, /* informational: reads re-run in the reference's double arithmetic (old/chaos_game.c:200-251) */
+  HPGQ_S_CG_MOVED_WORDS, /* informational: chaos-game words whose cell differs between the double and the integer form */
   HPGQ_S_COUNT = 32
 };
 

@@ -8,7 +8,7 @@ from test_oracle import (EDIT_OPTS, EDIT_READS, EDIT_TRIM, FILTER_MASK, FILTER_O
 
 pytestmark = pytest.mark.gpu
 
-IGNORE = ("SLOW_READS", "BATCHES", "CG_LONG_RUNS")
+IGNORE = ("SLOW_READS", "BATCHES", "CG_LONG_RUNS", "CG_FIXED_READS", "CG_MOVED_WORDS", "BAD_BATCH")
 
 
 def diff_report(q, lay, got, exp):
@@ -471,3 +471,43 @@ def test_compaction_checksum_matches_host_twin(q, ob):
     swapped[[0, 1]] = swapped[[1, 0]]
     if swapped[0] != swapped[1]:
         assert ck["checksum"] != q.checksum_host(swapped, cp["out_qual"], cp["out_idx"], cp["out_src"])
+
+
+@pytest.mark.parametrize("k", [2, 5, 10, 12])
+def test_chaos_game_exact_on_long_axis_runs(q, ob, k):
+    """Uncapped inputs (poly-T 70 + C-leading read, poly-G tails, runs with an N / a lower-case byte inside, runs
+    across read boundaries, single-axis short reads in a row): the CUDA tables equal the oracle's literal double
+    restatement AND the reference's own compiled chaos_game_fill_tables (oracle/_ref), cell for cell."""
+    from test_oracle import axis_run_batches
+    moved = 0
+    for seq, qual, idx in axis_run_batches(3) + axis_run_batches(11):
+        par = q.make_params(q.WORK_CHAOS, cg_k=k)
+        got, _, lay, _ = run_gpu(q, par, seq, qual, idx, 512, cg_k=k)
+        exp, _, _ = ob.process_batch(par, lay, seq, qual, idx)
+        for name in ("CG_SEQ", "CG_Q"):
+            assert np.array_equal(lay.section(got, name), lay.section(exp, name)), name
+        assert got[q.S["CG_WORDS"]] == exp[q.S["CG_WORDS"]]
+        moved += int(got[q.S["CG_MOVED_WORDS"]])
+        ref = ob.chaos_reference(seq, qual, idx, k)
+        if ref is not None:
+            assert np.array_equal(lay.section(got, "CG_SEQ").astype(np.uint32), ref[0])
+            assert np.array_equal((lay.section(got, "CG_Q") & 0xFFFFFFFF).astype(np.uint32), ref[1])
+    if k >= 5:
+        assert moved > 0, "the inputs must exercise the double / integer difference"
+
+
+def test_chaos_game_exact_inside_a_large_batch(q, ob):
+    """Long runs scattered through 60 000 ordinary reads (the warm-up of a flagged read starts from unknown state and
+    must meet the true one), several batches accumulated, k = 10 with k-mers alongside."""
+    rng = np.random.default_rng(21)
+    cfg = q.synth_cfg(150)
+    seq, qual, idx = q.synth_host(cfg, 0, 60000)
+    seq = seq.copy()
+    for r in rng.choice(60000, 400, replace=False):
+        o, L = int(idx[r]), int(idx[r + 1] - idx[r])
+        a = int(rng.integers(0, L - 50))
+        n = int(rng.integers(40, L - a))
+        seq[o + a:o + a + n] = rng.choice(np.frombuffer([b"AT", b"GT", b"T", b"A"][int(rng.integers(0, 4))], dtype=np.uint8), n)
+    par = q.make_params(q.WORK_KMERS | q.WORK_CHAOS, k2=11, cg_k=10)
+    got, *_ = check(q, ob, par, seq, qual, idx, 160, kmers=True, k2=11, cg_k=10)
+    assert got[q.S["CG_FIXED_READS"]] >= 400

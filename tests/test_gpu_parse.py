@@ -9,7 +9,7 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 FILTER = dict(min_read_length=50, min_read_quality=20, max_N=5)
-IGNORE = ("SLOW_READS", "BATCHES")
+IGNORE = ("SLOW_READS", "BATCHES", "CG_FIXED_READS", "CG_MOVED_WORDS", "BAD_BATCH")
 
 
 def make_text(seq, qual, idx, eol=b"\n", final_eol=True, hdr=lambda i: b"@read%d/%d len" % (i, i * 7919 % 1013)):

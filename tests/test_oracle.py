@@ -201,3 +201,66 @@ def test_oracle_golden_counters(q, ob):
         sec = lay.section(c, name).astype(object)
         assert int(sum(sec)) == s, name
         assert int(sum((i + 1) * int(v) for i, v in enumerate(sec)) % (1 << 61)) == wsum, name
+
+
+def axis_run_batches(seed=0):
+    """Inputs on which the reference's double arithmetic leaves the integer index (old/chaos_game.c:200-251): axis
+    runs of 40-120 bases (A/T, G/T, single letters) ending in and starting reads, crossing read boundaries, with an N
+    or a lower-case byte inside, short single-axis reads in a row, and random reads in between."""
+    rng = np.random.default_rng(seed)
+
+    def rnd(n, letters=b"ACGT"):
+        return bytes(int(x) for x in rng.choice(list(letters), n))
+
+    def ql(n):
+        return bytes(int(x) for x in rng.integers(35, 74, n))
+
+    out = []
+    # the survey's case: poly-T >= 60, then a C-leading read
+    reads = [b"T" * 70, b"C" * 12 + rnd(40), rnd(80), b"ACGT" + b"G" * 66, b"CA" + rnd(60)]
+    out.append(reads)
+    # runs ending a read and going on in the next, tails of every length, N and lower case inside
+    reads = []
+    for i in range(60):
+        run_letters = [b"AT", b"GT", b"T", b"A", b"G"][i % 5]
+        n1, n2 = int(rng.integers(15, 70)), int(rng.integers(0, 60))
+        reads.append(rnd(int(rng.integers(5, 60))) + rnd(n1, run_letters))
+        reads.append(rnd(n2, run_letters) + rnd(int(rng.integers(1, 40)), b"CG" if run_letters in (b"AT", b"T", b"A") else b"CA")
+                     + rnd(int(rng.integers(0, 50))))
+        if i % 7 == 0:
+            r = bytearray(rnd(90, run_letters))
+            r[30] = ord("N")
+            reads.append(bytes(r) + b"C" + rnd(30))
+        if i % 11 == 0:
+            r = bytearray(rnd(80, run_letters))
+            r[41] = ord("a")
+            reads.append(bytes(r) + rnd(20))
+        reads.append(rnd(int(rng.integers(20, 100))))
+    out.append(reads)
+    # short reads that lie on one axis throughout, in a row (no read holds a run of 21), then a lower move
+    reads = [rnd(int(rng.integers(8, 20)), b"AT") for _ in range(12)] + [b"CCG" + rnd(30)]
+    reads += [b"G" * 15 for _ in range(8)] + [b"A" + rnd(25), b"", b"N" * 5, b"T" * 300, b"C"]
+    out.append(reads)
+    return [pack([(r, ql(len(r))) for r in reads]) for reads in out]
+
+
+@pytest.mark.parametrize("k", [2, 5, 10, 12])
+def test_chaos_restatement_equals_reference_code_on_long_axis_runs(q, ob, k):
+    """The literal restatement against the reference's own compiled code where the double state matters; the integer
+    form must differ somewhere on these inputs (otherwise they would not exercise anything)."""
+    if ob.ref_lib() is None:
+        pytest.skip("oracle/_ref not built (reference tree absent on this machine)")
+    differs = False
+    for seq, qual, idx in axis_run_batches(3):
+        ts, tq, words = ob.chaos_literal(seq, qual, idx, k)
+        rs, rq, rwords = ob.chaos_reference(seq, qual, idx, k)
+        assert words == rwords
+        assert np.array_equal(ts.astype(np.uint32), rs)
+        assert np.array_equal((tq & 0xFFFFFFFF).astype(np.uint32), rq)
+        try:
+            its, itq, iw, _ = ob.chaos_int(seq, qual, idx, k)
+            differs |= not np.array_equal(its, ts)
+        except AssertionError:
+            pass  # the integer twin declines reads with foreign bytes
+    if k >= 5:
+        assert differs
