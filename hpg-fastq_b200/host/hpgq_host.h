@@ -45,6 +45,8 @@ typedef struct hq_options {
   char *quality_encoding_name;
   char *read_length_range, *read_quality_range, *left_quality_range, *right_quality_range;
   char *in_filename, *out_dirname;
+  char *in_filename1, *in_filename2; /* paired end (--fq1 / --fq2): the two mate files, run one after the other */
+  int paired;
   char *exec_name, *command_name;
   /* extensions of this implementation (not in the reference CLI) */
   int gpus;            /* --gpus N: batches dealt round-robin over N devices (default 1)            */

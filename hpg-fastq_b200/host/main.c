@@ -386,7 +386,13 @@ static int run_command(hq_options_t *o) {
   }
   r->device_parse = !o->host_parse;
   r->text_budget = 2 * cap_bytes; /* bases are less than half of the text, so a chunk never exceeds cap_bytes bases */
-  if (o->command == HQ_CMD_FILTER) {
+  if (o->paired && o->command != HQ_CMD_STATS) {
+    /* paired end: one .valid (and .invalid) file per mate file (old/README:78,115-118) */
+    const char *base = strrchr(o->in_filename, '/');
+    base = base ? base + 1 : o->in_filename;
+    snprintf(pass_name, sizeof pass_name, "%s/%s.valid", o->out_dirname, base);
+    if (o->command == HQ_CMD_FILTER || o->filter_on) snprintf(fail_name, sizeof fail_name, "%s/%s.invalid", o->out_dirname, base);
+  } else if (o->command == HQ_CMD_FILTER) {
     snprintf(pass_name, sizeof pass_name, "%s/passed.fq", o->out_dirname); /* src/filter_fastq.c:185 */
     snprintf(fail_name, sizeof fail_name, "%s/failed.fq", o->out_dirname); /* src/filter_fastq.c:189 */
   } else if (o->command == HQ_CMD_EDIT) {
@@ -512,11 +518,35 @@ int main(int argc, char *argv[]) {
     return 255; /* the reference exits with -1 here, src/hpg-fastq.c:30 */
   }
   const char *command_name = argv[1];
+  /* Action flags of the legacy generation (old/main_hpg_fastq_old.c:131-140, old/README:52,85,119): `hpg-fastq --qc`,
+   * `--filter`, `--prep` select stats / filter / edit; "if not flag at all only quality control is performed". */
+  char **largv = NULL;
+  if (command_name[0] == '-' && command_name[1] == '-') {
+    command_name = "stats";
+    largv = (char **)calloc((size_t)argc + 1, sizeof *largv);
+    if (!largv) return 255;
+    int n = 1;
+    for (int a = 1; a < argc; a++) {
+      if (!strcmp(argv[a], "--qc") || !strcmp(argv[a], "--quality-control")) command_name = "stats";
+      else if (!strcmp(argv[a], "--filter")) command_name = "filter";
+      else if (!strcmp(argv[a], "--prep") || !strcmp(argv[a], "--preprocessing")) command_name = "edit";
+      else largv[n++] = argv[a];
+    }
+    largv[0] = (char *)command_name;
+  }
+  int pargc = argc - 1;
+  char **pargv = argv + 1;
+  if (largv) {
+    pargc = 1;
+    while (largv[pargc]) pargc++;
+    pargv = largv;
+  }
   if (strcmp(command_name, "stats") && strcmp(command_name, "filter") && strcmp(command_name, "edit")) {
     usage(exec_name);
     return 255;
   }
-  hq_options_t *o = hq_options_parse(exec_name, command_name, argc - 1, argv + 1);
+  hq_options_t *o = hq_options_parse(exec_name, command_name, pargc, pargv);
+  free(largv);
   if (!o) return 255;
   if (!hq_options_validate(o)) {
     hq_options_free(o);
@@ -528,6 +558,13 @@ int main(int argc, char *argv[]) {
   }
   g_log = fopen("hpg-fastq.log", "w"); /* init_log_custom(..., "hpg-fastq.log", "w"), src/hpg-fastq.c:66 */
   int rc = run_command(o);
+  if (!rc && o->paired) {
+    /* second mate: an independent run of the same command ("the outputs are calculated seperately for both files",
+     * old/README:181).  A synchronised drop of both mates is described nowhere in the reference tree. */
+    free(o->in_filename);
+    o->in_filename = strdup(o->in_filename2);
+    rc = o->in_filename ? run_command(o) : 1;
+  }
   if (!rc) logf_("INFO", "Done !");
   if (g_log) fclose(g_log);
   hq_options_free(o);

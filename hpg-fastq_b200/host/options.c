@@ -49,6 +49,14 @@ static const hq_optdef_t OPTS[] = {
     {NULL, "chaos-game", A_INT, "[B200] chaos-game frequency matrices of this word size (eg. 10)", C_S, 1},
     {NULL, "host-parse", A_LIT, "[B200] cut the FastQ records on the host instead of on the GPU", C_ALL, 1},
     {NULL, "chaos-game-signature", A_STR, "[B200] genomic signature file (.gs) for the chaos-game difference image", C_S, 1},
+    /* paired-end input of the legacy generation (old/README:59-60, old/main_hpg_fastq_old.c:168-173): both mate
+     * files in one invocation, "the outputs are calculated seperately for both files" (old/README:181) */
+    {NULL, "fq1", A_STR, "[legacy] paired-end input, mate 1 (FastQ); with --fq2 instead of -f", C_ALL, 1},
+    {NULL, "fq2", A_STR, "[legacy] paired-end input, mate 2 (FastQ)", C_ALL, 1},
+    {NULL, "fastq1", A_STR, "[legacy] synonymous of --fq1", C_ALL, 1},
+    {NULL, "fastq2", A_STR, "[legacy] synonymous of --fq2", C_ALL, 1},
+    {NULL, "fq", A_STR, "[legacy] synonymous of --fastq-file", C_ALL, 1},
+    {NULL, "fastq", A_STR, "[legacy] synonymous of --fastq-file", C_ALL, 1},
 };
 #define N_OPTS ((int)(sizeof OPTS / sizeof OPTS[0]))
 
@@ -106,6 +114,8 @@ void hq_options_free(hq_options_t *o) {
   free(o->right_quality_range);
   free(o->cg_signature);
   free(o->in_filename);
+  free(o->in_filename1);
+  free(o->in_filename2);
   free(o->out_dirname);
   free(o->exec_name);
   free(o->command_name);
@@ -146,6 +156,9 @@ static int set_option(hq_options_t *o, int i, const char *val) {
     case 18: o->cg_k = iv; break;
     case 19: o->host_parse = 1; break;
     case 20: SETS(cg_signature); break;
+    case 21: case 23: SETS(in_filename1); break;
+    case 22: case 24: SETS(in_filename2); break;
+    case 25: case 26: SETS(in_filename); break;
     default: return 0;
   }
 #undef SETS
@@ -234,6 +247,21 @@ int hq_parse_range(int *min, int *max, const char *range, const char *msg) {
 
 int hq_options_validate(hq_options_t *o) {
   /* stats_options_validate(), src/stats_options.c:110-160 (filter/edit siblings are the same minus the encoding) */
+  if (o->in_filename1 || o->in_filename2) {
+    /* paired end: both mates are mandatory (old/README:59-60), and they replace -f */
+    if (!o->in_filename1 || !o->in_filename2 || o->in_filename) {
+      printf("\nError: paired-end input needs both --fq1 and --fq2 (and no --fastq-file)\n");
+      hq_usage(o->exec_name, o->command_name, o->command, stdout);
+      return 0;
+    }
+    if (!path_exists(o->in_filename1) || !path_exists(o->in_filename2)) {
+      printf("\nError: Input file name not found !\n");
+      hq_usage(o->exec_name, o->command_name, o->command, stdout);
+      return 0;
+    }
+    o->paired = 1;
+    o->in_filename = dupstr(o->in_filename1);
+  }
   if (!path_exists(o->in_filename)) {
     printf("\nError: Input file name not found !\n");
     hq_usage(o->exec_name, o->command_name, o->command, stdout);

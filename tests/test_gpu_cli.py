@@ -253,3 +253,43 @@ def test_device_parser_hands_irregular_input_back(q, fastq, tmp_path):
     assert "handed the input back" in log and " 0 device-parsed" not in log
     assert outs["dev"] == outs["host"]
     assert outs["dev"]["passed.fq"].count(b"\n+\n") + outs["dev"]["failed.fq"].count(b"\n+\n") == n
+
+
+def test_paired_end_invocation_equals_two_single_runs(q, fastq, tmp_path):
+    """SURVEY.md 8f rank 4, as far as the reference pins it: `--fq1 A --fq2 B` runs both mate files in one invocation
+    and "the outputs are calculated seperately for both files" (old/README:181): per-mate .valid / .invalid files
+    (old/README:78,115-118) equal passed.fq / failed.fq of single-file runs, per-mate report files equal the
+    single-file reports; the legacy action flags --filter / --qc select the command."""
+    f = fastq
+    n2 = 9000
+    m2 = str(tmp_path / "mate_2.fq")
+    hb.write_fastq(m2, [h.replace(b"/1", b"/2") for h in f["hdr"][:n2]], f["seq"], np.clip(f["qual"].astype(np.int32) - 2, 33, 126).astype(np.uint8),
+                   f["idx"][:n2 + 1])
+    singles = {}
+    for tag, path in (("a", f["path"]), ("b", m2)):
+        out = tmp_path / ("single_" + tag)
+        out.mkdir()
+        r = subprocess.run([hb.CLI, "filter", "-f", path, "-o", str(out)] + FILTER_ARGS, capture_output=True, text=True, cwd=str(out))
+        assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+        singles[tag] = out
+    out = tmp_path / "paired"
+    out.mkdir()
+    r = subprocess.run([hb.CLI, "--filter", "--fq1", f["path"], "--fastq2", m2, "-o", str(out)] + FILTER_ARGS, capture_output=True,
+                       text=True, cwd=str(out))
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+    for tag, path in (("a", f["path"]), ("b", m2)):
+        base = os.path.basename(path)
+        assert (out / (base + ".valid")).read_bytes() == (singles[tag] / "passed.fq").read_bytes()
+        assert (out / (base + ".invalid")).read_bytes() == (singles[tag] / "failed.fq").read_bytes()
+    assert r.stdout.count("Num. passed reads:") == 2
+    # stats (--qc): per-mate report files, identical to the single-file runs
+    reps = {}
+    for tag, args in (("one_a", ["stats", "-f", f["path"]]), ("one_b", ["stats", "-f", m2]), ("two", ["--qc", "--fq1", f["path"], "--fq2", m2])):
+        d = tmp_path / ("stats_" + tag)
+        d.mkdir()
+        r = subprocess.run([hb.CLI] + args + ["-o", str(d), "--kmers"], capture_output=True, text=True, cwd=str(d))
+        assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+        reps[tag] = _files(d)
+    both = dict(reps["one_a"])
+    both.update(reps["one_b"])
+    assert reps["two"] == both and len(both) == len(reps["one_a"]) + len(reps["one_b"])

@@ -317,3 +317,21 @@ def test_cli_fails_loudly_without_gpu(q, tmp_path):
     assert r.returncode == 255 and "Nothing to filter" in r.stdout
     r = subprocess.run([hb.CLI], capture_output=True, text=True)
     assert r.returncode == 255 and "Usage:" in r.stdout
+
+
+def test_paired_end_options(tmp_path):
+    """--fq1 / --fq2 (and the --fastq1 / --fastq2 synonyms, old/README:59-60): both mates or none, never with -f."""
+    import host_binding as hb
+    a, b = tmp_path / "m_1.fq", tmp_path / "m_2.fq"
+    a.write_bytes(b"@r\nACGT\n+\nIIII\n")
+    b.write_bytes(b"@r\nACGT\n+\nIIII\n")
+    for k1, k2 in (("--fq1", "--fq2"), ("--fastq1", "--fastq2")):
+        o = hb.Options("filter", [k1, str(a), k2, str(b), "--max-N", "1"])
+        assert o.valid and o.runnable
+        o.close()
+    assert not hb.Options("filter", ["--fq1", str(a), "--max-N", "1"]).valid
+    assert not hb.Options("filter", ["--fq1", str(a), "--fq2", str(b), "-f", str(a), "--max-N", "1"]).valid
+    assert not hb.Options("stats", ["--fq1", str(a), "--fq2", str(tmp_path / "missing.fq")]).valid
+    o = hb.Options("stats", ["--fq", str(a)])
+    assert o.valid
+    o.close()
