@@ -182,6 +182,8 @@ static void slot_free(hpgq_slot &s) {
   cudaFree(s.d_maxlen); cudaFreeHost(s.h_small);
   cudaFree(s.cb.scan); cudaFree(s.cb.block_sums); cudaFree(s.cb.out_seq); cudaFree(s.cb.out_qual);
   cudaFree(s.cb.out_idx); cudaFree(s.cb.out_src); cudaFree(s.cb.totals);
+  cudaFree(s.cb.fz_agg); cudaFree(s.cb.fz_incl); cudaFree(s.cb.fz_status);
+  cudaFree(s.cb.fail_seq); cudaFree(s.cb.fail_qual); cudaFree(s.cb.fail_idx); cudaFree(s.cb.fail_src);
   cudaFreeHost(s.h_out_seq); cudaFreeHost(s.h_out_qual); cudaFreeHost(s.h_out_idx); cudaFreeHost(s.h_out_src);
   cudaFreeHost(s.h_lens);
   cudaFree(s.d_text); cudaFreeHost(s.h_text); cudaFreeHost(s.h_pinfo);

@@ -5,8 +5,10 @@
 //
 // Three steps: per-read (bytes, count) records -> exclusive scan (block scan + block-sum scan +
 // add) -> warp-per-read copy of seq and qual bytes to their final offsets.
+#include <stdlib.h>
 #include "hpgq_dev.cuh"
 #include "hpgq_internal.h"
+#include "hpgq_regs.cuh"
 #include "../../include/hpgq_synth.h"
 
 namespace {
@@ -244,6 +246,108 @@ __device__ __forceinline__ uint4 range_mask16(uint32_t lo, uint32_t hi) {
 
 __host__ __device__ constexpr uint32_t ct_rmap_bytes(uint32_t cap) { return ((cap >> 4) + 8u + 15u) & ~15u; }
 
+// Builds the aligned 16-byte chunks of a tile's two output spans (stream 0 = passed, 1 = failed) from the staged
+// source bytes and stores them to oseq[stream] / oqual[stream]; h.key[stream][r] is the offset of read r inside that
+// stream's buffer, rmap the chunk -> read map (failed span's entries mo_f behind the passed span's).
+__device__ __forceinline__ void ct_emit(const ct_hdr &h, const uint8_t *rmap, uint32_t mo_f, const uint8_t *sseq,
+                                        const uint8_t *squal, uint32_t nt, uint8_t *const oseq[2], uint8_t *const oqual[2]) {
+  const uint32_t tid = threadIdx.x;
+#pragma unroll 1
+  for (int stream = 0; stream < 2; ++stream) {
+    const uint32_t *key = h.key[stream];
+    const uint32_t D0 = key[0], D1 = key[nt];
+    if (D1 == D0) continue;
+    // a warp owns a contiguous run of the span's chunks, so the read index only moves forward between its rounds
+    const uint32_t c_lo = D0 >> 4, c_hi = (D1 + 15u) >> 4;
+    const uint32_t per = (c_hi - c_lo + 7u) >> 3;
+    const uint32_t w_lo = c_lo + (tid >> 5) * per, w_hi = min(c_hi, w_lo + per);
+    const uint8_t *mp = rmap + (stream ? mo_f : 0u) - c_lo;
+    for (uint32_t c = w_lo + (tid & 31u); c < w_hi; c += 32u) {
+      const uint32_t dc = c << 4, d0 = max(dc, D0), d1 = min(dc + 16u, D1);
+      const uint32_t r = mp[c];
+      const uint32_t kend = key[r + 1];
+      // first source: read r; second source: the next non-empty read of this stream when the chunk straddles
+      const uint32_t e1 = min(d1, kend);
+      const uint32_t x1 = h.soff[r] + (dc - key[r]);  // staged byte that lands on byte 0 of the chunk (mod 2^32)
+      uint32_t x2 = x1, e2 = d1, r2 = r;
+      if (e1 < d1) {
+        r2 = c + 1u < c_hi ? (uint32_t)mp[c + 1u] : r + 1u;  // usually the owner of the next chunk
+        uint32_t k2 = key[r2 + 1];
+        if (__builtin_expect(key[r2] != kend || k2 <= kend, 0)) {  // a read shorter than the rest of this chunk
+          r2 = r + 1u;
+          k2 = key[r2 + 1];
+          while (k2 <= e1) k2 = key[++r2 + 1];
+        }
+        x2 = h.soff[r2] + (dc - key[r2]);
+        e2 = min(d1, k2);
+      }
+      // Reads that follow each other in the input AND in this stream untrimmed keep their distance: then the chunk's
+      // second source is the continuation of the first (x2 == x1) and one shifted 32-byte window gives all 16 bytes.
+      uint4 vs, vq;
+      {
+        const uint32_t xa = x1 & ~15u;
+        const uint4 As = *reinterpret_cast<const uint4 *>(sseq + xa), Bs = *reinterpret_cast<const uint4 *>(sseq + xa + 16u);
+        const uint4 Aq = *reinterpret_cast<const uint4 *>(squal + xa), Bq = *reinterpret_cast<const uint4 *>(squal + xa + 16u);
+        vs = shift_sel(As, Bs, x1 & 15u);
+        vq = shift_sel(Aq, Bq, x1 & 15u);
+      }
+      if (__builtin_expect(x2 != x1, 0)) {
+        const uint32_t xb = x2 & ~15u;
+        const uint4 Cs = *reinterpret_cast<const uint4 *>(sseq + xb), Ds = *reinterpret_cast<const uint4 *>(sseq + xb + 16u);
+        const uint4 Cq = *reinterpret_cast<const uint4 *>(squal + xb), Dq = *reinterpret_cast<const uint4 *>(squal + xb + 16u);
+        const uint4 ts = shift_sel(Cs, Ds, x2 & 15u), tq = shift_sel(Cq, Dq, x2 & 15u);
+        const uint4 m = range_mask16(0u, e1 - dc);  // bytes of the first source
+        vs = make_uint4((vs.x & m.x) | (ts.x & ~m.x), (vs.y & m.y) | (ts.y & ~m.y), (vs.z & m.z) | (ts.z & ~m.z),
+                        (vs.w & m.w) | (ts.w & ~m.w));
+        vq = make_uint4((vq.x & m.x) | (tq.x & ~m.x), (vq.y & m.y) | (tq.y & ~m.y), (vq.z & m.z) | (tq.z & ~m.z),
+                        (vq.w & m.w) | (tq.w & ~m.w));
+      }
+      if (__builtin_expect(e2 < d1, 0)) {  // three or more reads in one chunk (reads shorter than 16 bytes)
+        uint32_t d = e2, rr = r2 + 1u;
+        while (d < d1) {
+          uint32_t k3 = key[rr + 1];
+          while (k3 <= d) k3 = key[++rr + 1];
+          const uint32_t e = min(d1, k3);
+          const uint32_t x = h.soff[rr] + (dc - key[rr]);
+          const uint32_t xa = x & ~15u;
+          const uint4 As = *reinterpret_cast<const uint4 *>(sseq + xa), Bs = *reinterpret_cast<const uint4 *>(sseq + xa + 16u);
+          const uint4 Aq = *reinterpret_cast<const uint4 *>(squal + xa), Bq = *reinterpret_cast<const uint4 *>(squal + xa + 16u);
+          const uint4 ps = shift_sel(As, Bs, x & 15u), pq = shift_sel(Aq, Bq, x & 15u);
+          const uint4 m = range_mask16(d - dc, e - dc);
+          vs.x = (vs.x & ~m.x) | (ps.x & m.x); vs.y = (vs.y & ~m.y) | (ps.y & m.y);
+          vs.z = (vs.z & ~m.z) | (ps.z & m.z); vs.w = (vs.w & ~m.w) | (ps.w & m.w);
+          vq.x = (vq.x & ~m.x) | (pq.x & m.x); vq.y = (vq.y & ~m.y) | (pq.y & m.y);
+          vq.z = (vq.z & ~m.z) | (pq.z & m.z); vq.w = (vq.w & ~m.w) | (pq.w & m.w);
+          d = e;
+          ++rr;
+        }
+      }
+      if (d1 - d0 == 16u) {
+        *reinterpret_cast<uint4 *>(oseq[stream] + dc) = vs;
+        *reinterpret_cast<uint4 *>(oqual[stream] + dc) = vq;
+      } else {  // first / last chunk of the span: its other bytes belong to a neighbouring tile
+        const uint32_t ws[4] = {vs.x, vs.y, vs.z, vs.w}, wq[4] = {vq.x, vq.y, vq.z, vq.w};
+        const uint32_t vlo = d0 - dc, vhi = d1 - dc;
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+          const uint32_t w0 = 4u * w;
+          if (vlo <= w0 && vhi >= w0 + 4u) {
+            *reinterpret_cast<uint32_t *>(oseq[stream] + dc + w0) = ws[w];
+            *reinterpret_cast<uint32_t *>(oqual[stream] + dc + w0) = wq[w];
+          } else if (vlo < w0 + 4u && vhi > w0) {
+#pragma unroll
+            for (int t = 0; t < 4; ++t)
+              if (w0 + t >= vlo && w0 + t < vhi) {
+                oseq[stream][dc + w0 + t] = (uint8_t)(ws[w] >> (8 * t));
+                oqual[stream][dc + w0 + t] = (uint8_t)(wq[w] >> (8 * t));
+              }
+          }
+        }
+      }
+    }
+  }
+}
+
 __global__ void __launch_bounds__(256) hq_compact_copy_tile(hq_kargs a, hq_compact_bufs b, uint32_t rpt, uint32_t cap) {
   extern __shared__ __align__(16) uint8_t ct_raw[];
   ct_hdr &h = *reinterpret_cast<ct_hdr *>(ct_raw);
@@ -288,96 +392,445 @@ __global__ void __launch_bounds__(256) hq_compact_copy_tile(hq_kargs a, hq_compa
       reinterpret_cast<uint4 *>(squal + CT_PAD)[c] = __ldg(reinterpret_cast<const uint4 *>(a.qual + S0a) + c);
     }
     __syncthreads();
-#pragma unroll 1
-    for (int stream = 0; stream < 2; ++stream) {
-      const uint32_t *key = h.key[stream];
-      const uint32_t D0 = key[0], D1 = key[nt];
-      if (D1 == D0) continue;
-      // a warp owns a contiguous run of the span's chunks, so the read index only moves forward between its rounds
-      const uint32_t c_lo = D0 >> 4, c_hi = (D1 + 15u) >> 4;
-      const uint32_t per = (c_hi - c_lo + 7u) >> 3;
-      const uint32_t w_lo = c_lo + (tid >> 5) * per, w_hi = min(c_hi, w_lo + per);
-      const uint8_t *mp = rmap + (stream ? mo_f : 0u) - c_lo;
-      for (uint32_t c = w_lo + (tid & 31u); c < w_hi; c += 32u) {
-        const uint32_t dc = c << 4, d0 = max(dc, D0), d1 = min(dc + 16u, D1);
-        const uint32_t r = mp[c];
-        const uint32_t kend = key[r + 1];
-        // first source: read r; second source: the next non-empty read of this stream when the chunk straddles
-        const uint32_t e1 = min(d1, kend);
-        const uint32_t x1 = h.soff[r] + (dc - key[r]);  // staged byte that lands on byte 0 of the chunk (mod 2^32)
-        uint32_t x2 = x1, e2 = d1, r2 = r;
-        if (e1 < d1) {
-          r2 = c + 1u < c_hi ? (uint32_t)mp[c + 1u] : r + 1u;  // usually the owner of the next chunk
-          uint32_t k2 = key[r2 + 1];
-          if (__builtin_expect(key[r2] != kend || k2 <= kend, 0)) {  // a read shorter than the rest of this chunk
-            r2 = r + 1u;
-            k2 = key[r2 + 1];
-            while (k2 <= e1) k2 = key[++r2 + 1];
-          }
-          x2 = h.soff[r2] + (dc - key[r2]);
-          e2 = min(d1, k2);
-        }
-        uint4 vs, vq;
-        {
-          const uint32_t xa = x1 & ~15u, xb = x2 & ~15u;
-          const uint4 As = *reinterpret_cast<const uint4 *>(sseq + xa), Bs = *reinterpret_cast<const uint4 *>(sseq + xa + 16u);
-          const uint4 Aq = *reinterpret_cast<const uint4 *>(squal + xa), Bq = *reinterpret_cast<const uint4 *>(squal + xa + 16u);
-          const uint4 Cs = *reinterpret_cast<const uint4 *>(sseq + xb), Ds = *reinterpret_cast<const uint4 *>(sseq + xb + 16u);
-          const uint4 Cq = *reinterpret_cast<const uint4 *>(squal + xb), Dq = *reinterpret_cast<const uint4 *>(squal + xb + 16u);
-          const uint4 ps = shift_sel(As, Bs, x1 & 15u), pq = shift_sel(Aq, Bq, x1 & 15u);
-          const uint4 ts = shift_sel(Cs, Ds, x2 & 15u), tq = shift_sel(Cq, Dq, x2 & 15u);
-          const uint4 m = range_mask16(0u, e1 - dc);  // bytes of the first source
-          vs = make_uint4((ps.x & m.x) | (ts.x & ~m.x), (ps.y & m.y) | (ts.y & ~m.y), (ps.z & m.z) | (ts.z & ~m.z),
-                          (ps.w & m.w) | (ts.w & ~m.w));
-          vq = make_uint4((pq.x & m.x) | (tq.x & ~m.x), (pq.y & m.y) | (tq.y & ~m.y), (pq.z & m.z) | (tq.z & ~m.z),
-                          (pq.w & m.w) | (tq.w & ~m.w));
-        }
-        if (__builtin_expect(e2 < d1, 0)) {  // three or more reads in one chunk (reads shorter than 16 bytes)
-          uint32_t d = e2, rr = r2 + 1u;
-          while (d < d1) {
-            uint32_t k3 = key[rr + 1];
-            while (k3 <= d) k3 = key[++rr + 1];
-            const uint32_t e = min(d1, k3);
-            const uint32_t x = h.soff[rr] + (dc - key[rr]);
-            const uint32_t xa = x & ~15u;
-            const uint4 As = *reinterpret_cast<const uint4 *>(sseq + xa), Bs = *reinterpret_cast<const uint4 *>(sseq + xa + 16u);
-            const uint4 Aq = *reinterpret_cast<const uint4 *>(squal + xa), Bq = *reinterpret_cast<const uint4 *>(squal + xa + 16u);
-            const uint4 ps = shift_sel(As, Bs, x & 15u), pq = shift_sel(Aq, Bq, x & 15u);
-            const uint4 m = range_mask16(d - dc, e - dc);
-            vs.x = (vs.x & ~m.x) | (ps.x & m.x); vs.y = (vs.y & ~m.y) | (ps.y & m.y);
-            vs.z = (vs.z & ~m.z) | (ps.z & m.z); vs.w = (vs.w & ~m.w) | (ps.w & m.w);
-            vq.x = (vq.x & ~m.x) | (pq.x & m.x); vq.y = (vq.y & ~m.y) | (pq.y & m.y);
-            vq.z = (vq.z & ~m.z) | (pq.z & m.z); vq.w = (vq.w & ~m.w) | (pq.w & m.w);
-            d = e;
-            ++rr;
-          }
-        }
-        if (d1 - d0 == 16u) {
-          *reinterpret_cast<uint4 *>(b.out_seq + dc) = vs;
-          *reinterpret_cast<uint4 *>(b.out_qual + dc) = vq;
-        } else {  // first / last chunk of the span: its other bytes belong to a neighbouring tile
-          const uint32_t ws[4] = {vs.x, vs.y, vs.z, vs.w}, wq[4] = {vq.x, vq.y, vq.z, vq.w};
-          const uint32_t vlo = d0 - dc, vhi = d1 - dc;
+    uint8_t *const oseq[2] = {b.out_seq, b.out_seq}, *const oqual[2] = {b.out_qual, b.out_qual};
+    ct_emit(h, rmap, mo_f, sseq, squal, nt, oseq, oqual);
+  }
+  if (blockIdx.x == 0 && tid == 0) b.out_idx[n] = tot.x + tot.y;
+}
+
+// ---------------------------------------------------------------- edit + filter + compaction in ONE pass over HBM
+// fastq_edit_worker / fastq_filter_worker (src/edit_fastq.c:142-178, src/filter_fastq.c:134-155) and the consumers'
+// fastq_fwrite of the passed / failed lists (src/edit_fastq.c:184-206, src/filter_fastq.c:161-174) for one batch.
+// A CTA draws tiles of <= 128 consecutive reads in input order (ticket counter).  Per tile: (A) the tile's source span
+// is staged in shared memory -- the only time the batch is read from HBM; (B) lane groups take the trim and filter
+// decisions from the staged bytes (the register-resident code of hpgq_regs.cuh); (C) one warp scans the tile's
+// (passed bytes, failed bytes, passed reads, failed reads); (D) a decoupled look-back over the preceding tiles'
+// published aggregates turns that into the tile's place in the output; (E, F) the chunks of the passed span go
+// straight to their final place, those of the failed span to a side buffer, because the failed reads follow ALL
+// passed reads of the batch and that total is only known at the end: hq_fz_finish moves the side buffer (a few
+// per cent of the bytes) behind the passed reads.  DRAM traffic: 2 L + 4 in, 2 L' + 17 out per read.
+__device__ __forceinline__ void fz_cp16(void *dst_smem, const void *src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst_smem)), "l"(src)
+               : "memory");
+}
+// Look-back records.  A tile publishes its own totals and, once it knows them, the totals of everything up to and
+// including itself, each as four 64-bit words {value, 1}: a word is written once and carries its own validity, so
+// neither side needs a memory fence (a __threadfence here waits for the CTA's output stores: 40 % of the kernel).
+struct fz_rec {
+  unsigned long long w[4];
+};
+__device__ __forceinline__ void fz_publish(fz_rec *r, uint4 v) {
+  volatile unsigned long long *p = r->w;
+  p[0] = (1ull << 32) | v.x;
+  p[1] = (1ull << 32) | v.y;
+  p[2] = (1ull << 32) | v.z;
+  p[3] = (1ull << 32) | v.w;
+}
+__device__ __forceinline__ bool fz_read(const fz_rec *r, uint4 *v) {
+  const volatile unsigned long long *p = r->w;
+  const unsigned long long a0 = p[0], a1 = p[1], a2 = p[2], a3 = p[3];
+  *v = make_uint4((uint32_t)a0, (uint32_t)a1, (uint32_t)a2, (uint32_t)a3);
+  return ((a0 & a1 & a2 & a3) >> 32) != 0ull;
+}
+struct fz_bufs {
+  fz_rec *agg, *incl;       // per tile: its own totals / the totals of all tiles up to and including it
+  uint32_t *status;         // status[0] = ticket counter
+  uint8_t *fail_seq, *fail_qual;
+  uint32_t *fail_idx, *fail_src;
+  uint32_t n_tiles, rpt, cap;
+};
+
+struct fz_hdr {
+  ct_hdr ct;
+  uint32_t sidx[CT_RPT + 1];   // offsets of the tile's reads
+  uint32_t start[CT_RPT], len[CT_RPT];
+  uint8_t pass[CT_RPT];
+  uint4 prefix;                // totals of all preceding tiles
+  uint32_t tile;
+};
+
+// Trim + filter decision of one read by the G lanes of its group, the read held in registers (32 bytes per lane):
+// takes every option (filter windows, out-of-quality count).  o = batch offset of the read, L = its length; the
+// staged copy of batch byte x lies at squal / sseq [x - S0a + CT_PAD].
+struct fz_dec {
+  uint32_t start, len;
+  bool pass, edited;
+};
+template <int G, bool OOQ>
+__device__ __forceinline__ fz_dec fz_decide_regs(const hq_kargs &a, const uint8_t *sseq, const uint8_t *squal, uint32_t S0a,
+                                             uint32_t o, uint32_t L, uint32_t lig, bool do_edit, bool do_filter,
+                                             bool zero_is_ooq) {
+  bool edited_any = false;
+  rg_read d;
+  d.c = (o & ~15u) + RG_LB * lig;
 #pragma unroll
-          for (int w = 0; w < 4; ++w) {
-            const uint32_t w0 = 4u * w;
-            if (vlo <= w0 && vhi >= w0 + 4u) {
-              *reinterpret_cast<uint32_t *>(b.out_seq + dc + w0) = ws[w];
-              *reinterpret_cast<uint32_t *>(b.out_qual + dc + w0) = wq[w];
-            } else if (vlo < w0 + 4u && vhi > w0) {
+  for (int k = 0; k < RG_CPL; ++k) {
+    uint4 q4 = make_uint4(0, 0, 0, 0), s4 = q4;
+    if (d.c + 16u * k < o + L) {
+      const uint32_t x = d.c + 16u * k - S0a + CT_PAD;
+      q4 = *reinterpret_cast<const uint4 *>(squal + x);
+      s4 = *reinterpret_cast<const uint4 *>(sseq + x);
+    }
+    d.q[4 * k + 0] = q4.x; d.q[4 * k + 1] = q4.y; d.q[4 * k + 2] = q4.z; d.q[4 * k + 3] = q4.w;
+    d.s[4 * k + 0] = s4.x; d.s[4 * k + 1] = s4.y; d.s[4 * k + 2] = s4.z; d.s[4 * k + 3] = s4.w;
+  }
+  uint32_t start = 0, len = L;
+  if (do_edit) {  // fastq_edit: a window whose mean quality is out of range is cut off
+    bool edited = false;
+    if (a.e_ll > 0) {
+      const uint32_t w = min((uint32_t)a.e_ll, len);
+      const uint32_t sw = group_sum<G>(rg_window_lane(d, o, o + w));
+      if (w && !mean_ok32(sw, w, a.e_lq_lo, a.e_lq_hi)) {
+        start += w;
+        len -= w;
+        edited = true;
+      }
+    }
+    if (a.e_rl > 0) {
+      const uint32_t w = min((uint32_t)a.e_rl, len);
+      const uint32_t e = o + start + len;
+      const uint32_t sw = group_sum<G>(rg_window_lane(d, e - w, e));
+      if (w && !mean_ok32(sw, w, a.e_rq_lo, a.e_rq_hi)) {
+        len -= w;
+        edited = true;
+      }
+    }
+    edited_any = edited;
+  }
+  rg_clip(d, o + start, o + start + len);
+  const uint32_t b0 = o + start, b1 = b0 + len;
+  bool pass = true;
+  if (do_filter) {
+    uint32_t S = 0, fN = 0, fO = 0, hib = 0;
 #pragma unroll
-              for (int t = 0; t < 4; ++t)
-                if (w0 + t >= vlo && w0 + t < vhi) {
-                  b.out_seq[dc + w0 + t] = (uint8_t)(ws[w] >> (8 * t));
-                  b.out_qual[dc + w0 + t] = (uint8_t)(wq[w] >> (8 * t));
-                }
-            }
+    for (int j = 0; j < RG_W; ++j) {
+      const uint32_t qw = d.q[j], sw = d.s[j];
+      S = __dp4a(qw, 0x01010101u, S);
+      fN += rg_zero_flags(sw ^ 0x4E4E4E4Eu) >> 7;
+      if (OOQ) {
+        fO += (~((qw + a.c_lo) & ~(qw + a.c_hi)) & 0x80808080u) >> 7;
+        hib |= qw;
+      }
+    }
+    uint32_t nN = __dp4a(fN, 0x01010101u, 0u), ooq = __dp4a(fO, 0x01010101u, 0u);
+    if (OOQ && zero_is_ooq) {  // remove the lane's zeroed bytes from the out-of-range count
+      const uint32_t lo = max(b0, d.c), hi = min(b1, d.c + RG_LB);
+      ooq -= RG_LB - (hi > lo ? hi - lo : 0u);
+    }
+    if (OOQ && (hib & 0x80808080u)) {  // a quality byte >= 128: exact per-byte count for this lane
+      ooq = 0;
+      for (int j = 0; j < RG_W; ++j)
+        for (int i = 0; i < 4; ++i) {
+          const uint32_t pos = d.c + 4u * j + i;
+          const int32_t qq = (int32_t)((d.q[j] >> (8 * i)) & 0xFFu);
+          if (pos >= b0 && pos < b1) ooq += (qq < a.q_lo) | (qq > a.q_hi);
+        }
+    }
+    uint32_t p1 = group_sum<G>(S | (nN << 20));
+    if (OOQ) ooq = group_sum<G>(ooq);
+    S = p1 & 0xFFFFFu;
+    nN = p1 >> 20;
+    pass = (int32_t)len >= a.min_len && (int32_t)len <= a.max_len && mean_ok32(S, len, a.q_lo, a.q_hi) &&
+           (!OOQ || (int32_t)ooq <= a.max_ooq) && (int32_t)nN <= a.max_n;
+    if (a.f_ll > 0) {
+      const uint32_t wl = min((uint32_t)a.f_ll, len);
+      const uint32_t SL = group_sum<G>(rg_window_lane(d, b0, b0 + wl));
+      if (wl) pass = pass && mean_ok32(SL, wl, a.f_lq_lo, a.f_lq_hi);
+    }
+    if (a.f_rl > 0) {
+      const uint32_t wr = min((uint32_t)a.f_rl, len);
+      const uint32_t SR = group_sum<G>(rg_window_lane(d, b1 - wr, b1));
+      if (wr) pass = pass && mean_ok32(SR, wr, a.f_rq_lo, a.f_rq_hi);
+    }
+  }
+  return fz_dec{start, len, pass, edited_any};
+}
+
+// The same decision for the common case -- no filter windows, no out-of-quality limit, trim windows of <= 255 bases
+// that do not overlap (L >= left + right window) -- in the word frame of the tiled statistics kernel: lane lig owns
+// the words {lig + k G} of the read, byte masks of the read end and of the two trim windows are per-LENGTH constants
+// held in registers, and every sum is a dp4a.  Returns false in `ok` for a read it does not take (the caller then
+// runs fz_decide_regs for the warp).
+template <int K, int G>
+struct fz_len_consts {
+  uint32_t L, wl, wr;
+  uint32_t m[K], m01[K], ml[K], mr[K];  // read bytes (0xFF form, 0x01 form), left / right trim window (0x01 form)
+};
+template <int K, int G>
+__device__ __forceinline__ void fz_len_update(const hq_kargs &a, fz_len_consts<K, G> &c, uint32_t L, uint32_t lig) {
+  c.L = L;
+  c.wl = a.e_ll > 0 ? min((uint32_t)a.e_ll, L) : 0u;
+  c.wr = a.e_rl > 0 ? min((uint32_t)a.e_rl, L) : 0u;
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    const uint32_t p = 4u * ((uint32_t)k * G + lig);
+    c.m[k] = hq_tail_mask(p, L);
+    c.m01[k] = c.m[k] & 0x01010101u;
+    c.ml[k] = hq_range_ones(p, 0u, c.wl);
+    c.mr[k] = hq_range_ones(p, L - c.wr, L);
+  }
+}
+template <int K, int G>
+__device__ __forceinline__ fz_dec fz_decide_fast(const hq_kargs &a, const fz_len_consts<K, G> &c, const uint32_t *ps,
+                                                 const uint32_t *pq, uint32_t bsel, bool do_edit, bool do_filter) {
+  uint32_t S = 0, nN = 0, SL = 0, SR = 0, NL = 0, NR = 0;
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    const uint32_t sw = hq_prmt_raw(ps[k * G], ps[k * G + 1], bsel);
+    const uint32_t q = hq_prmt_raw(pq[k * G], pq[k * G + 1], bsel) & c.m[k];
+    const uint32_t z = (rg_zero_flags(sw ^ 0x4E4E4E4Eu) >> 7) & c.m01[k];  // 0x01 per 'N' of the read
+    S = __dp4a(q, 0x01010101u, S);
+    nN = __dp4a(z, 0x01010101u, nN);
+    SL = __dp4a(q, c.ml[k], SL);
+    SR = __dp4a(q, c.mr[k], SR);
+    NL = __dp4a(z, c.ml[k], NL);
+    NR = __dp4a(z, c.mr[k], NR);
+  }
+  // reads of at most 4 K G <= 640 bases, windows of at most 255: S < 2^18, counts < 2^10, window sums < 2^16
+  const uint32_t p1 = group_sum<G>(S | (nN << 20));
+  S = p1 & 0xFFFFFu;
+  nN = p1 >> 20;
+  uint32_t start = 0, len = c.L;
+  bool edited = false;
+  if (do_edit) {
+    const uint32_t p2 = group_sum<G>(SL | (NL << 16)), p3 = group_sum<G>(SR | (NR << 16));
+    if (c.wl && !mean_ok32(p2 & 0xFFFFu, c.wl, a.e_lq_lo, a.e_lq_hi)) {
+      start = c.wl;
+      len -= c.wl;
+      S -= p2 & 0xFFFFu;
+      nN -= p2 >> 16;
+      edited = true;
+    }
+    if (c.wr && !mean_ok32(p3 & 0xFFFFu, c.wr, a.e_rq_lo, a.e_rq_hi)) {
+      len -= c.wr;
+      S -= p3 & 0xFFFFu;
+      nN -= p3 >> 16;
+      edited = true;
+    }
+  }
+  bool pass = true;
+  if (do_filter)
+    pass = (int32_t)len >= a.min_len && (int32_t)len <= a.max_len && mean_ok32(S, len, a.q_lo, a.q_hi) && (int32_t)nN <= a.max_n;
+  return fz_dec{start, len, pass, edited};
+}
+
+// FAST: fz_decide_fast takes the reads (K words per lane), fz_decide_regs only those it declines.
+template <int K, int G, bool OOQ, bool FAST>
+__global__ void __launch_bounds__(256, 4) hq_fz_kernel(hq_kargs a, hq_compact_bufs b, fz_bufs z) {
+  extern __shared__ __align__(16) uint8_t fz_raw[];
+  fz_hdr &h = *reinterpret_cast<fz_hdr *>(fz_raw);
+  constexpr uint32_t HDR = (sizeof(fz_hdr) + 15u) & ~15u;
+  uint8_t *rmap = fz_raw + HDR;
+  uint8_t *sseq = rmap + ct_rmap_bytes(z.cap), *squal = sseq + z.cap;
+  constexpr uint32_t NG = 32u / G;
+  const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5, lig = lane % G, giw = lane / G;
+  const uint32_t n = a.n_reads, rpt = z.rpt;
+  const bool do_filter = a.work & HPGQ_WORK_FILTER, do_edit = a.work & HPGQ_WORK_EDIT;
+  const bool zero_is_ooq = a.q_lo > 0 || a.q_hi < 0;
+  uint32_t n_pass = 0, n_fail = 0, n_edit = 0;
+  fz_len_consts<K, G> lc;
+  lc.L = 0xFFFFFFFFu;
+  lc.wl = lc.wr = 0u;
+  for (;;) {
+    __syncthreads();  // the previous tile's shared memory is no longer read
+    if (tid == 0) h.tile = atomicAdd(&z.status[0], 1u);
+    __syncthreads();
+    const uint32_t tile = h.tile;
+    if (tile >= z.n_tiles) break;
+    const uint32_t i0 = tile * rpt, i1 = min(n, i0 + rpt), nt = i1 - i0;
+    // ---- A: offsets and source span into shared memory
+    for (uint32_t r = tid; r <= nt; r += 256u) h.sidx[r] = a.idx[i0 + r];
+    const uint32_t S0a = a.idx[i0] & ~15u, S1 = a.idx[i1];
+    const uint32_t nb16 = (S1 - S0a + 15u) >> 4;
+    for (uint32_t c = tid; c < nb16; c += 256u) {  // 16-byte cp.async: every chunk of the tile in flight at once
+      fz_cp16(sseq + CT_PAD + 16u * c, a.seq + S0a + 16u * c);
+      fz_cp16(squal + CT_PAD + 16u * c, a.qual + S0a + 16u * c);
+    }
+    asm volatile("cp.async.wait_all;" ::: "memory");
+    __syncthreads();
+    // ---- B: trim + filter decisions, G lanes per read, from the staged bytes
+    for (uint32_t rb = warp * NG; rb < nt; rb += 8u * NG) {  // warp-uniform trip count (shuffles below)
+      const uint32_t r = rb + giw;
+      const bool live = r < nt;
+      const uint32_t o = live ? h.sidx[r] : S0a, L = live ? h.sidx[r + 1] - o : 0u;
+      fz_dec dec;
+      bool slow = !FAST;
+      if (FAST) {
+        if (L != lc.L) fz_len_update<K, G>(a, lc, L, lig);
+        slow = lc.wl + lc.wr > L;  // overlapping trim windows: the right one moves with the left trim
+        const uint32_t so = o - S0a + CT_PAD;
+        const uint32_t *ps = reinterpret_cast<const uint32_t *>(sseq) + (so >> 2) + lig;
+        const uint32_t *pq = reinterpret_cast<const uint32_t *>(squal) + (so >> 2) + lig;
+        dec = fz_decide_fast<K, G>(a, lc, ps, pq, 0x3210u + 0x1111u * (so & 3u), do_edit, do_filter);
+      }
+      if (__any_sync(0xFFFFFFFFu, slow)) {
+        const fz_dec d2 = fz_decide_regs<G, OOQ>(a, sseq, squal, S0a, o, L, lig, do_edit, do_filter, zero_is_ooq);
+        if (slow) dec = d2;
+      }
+      const uint32_t start = dec.start, len = dec.len;
+      const bool pass = dec.pass;
+      if (live && lig == 0) {
+        n_edit += dec.edited;
+        if (do_filter) {
+          n_pass += pass;
+          n_fail += !pass;
+        }
+      }
+      if (live && lig == 0) {
+        h.start[r] = start;
+        h.len[r] = len;
+        h.pass[r] = pass ? 1 : 0;
+        if (a.trim) a.trim[i0 + r] = hpgq_trim_t{start, len};
+        if (a.mask) a.mask[i0 + r] = pass ? 1 : 0;
+      }
+    }
+    __syncthreads();
+    // ---- C + D: tile scan (warp 0, four reads per lane) and decoupled look-back
+    if (warp == 0) {
+      uint4 v[4], sum = make_uint4(0, 0, 0, 0);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const uint32_t r = 4u * lane + k;
+        v[k] = make_uint4(0, 0, 0, 0);
+        if (r < nt) v[k] = h.pass[r] ? make_uint4(h.len[r], 0, 1, 0) : make_uint4(0, h.len[r], 0, 1);
+        sum = add4(sum, v[k]);
+      }
+      uint4 inc = sum;
+#pragma unroll
+      for (int dd = 1; dd < 32; dd <<= 1) {
+        const uint4 u = shfl_up4(inc, dd);
+        if ((int)lane >= dd) inc = add4(inc, u);
+      }
+      const uint4 agg = make_uint4(__shfl_sync(0xFFFFFFFFu, inc.x, 31), __shfl_sync(0xFFFFFFFFu, inc.y, 31),
+                                   __shfl_sync(0xFFFFFFFFu, inc.z, 31), __shfl_sync(0xFFFFFFFFu, inc.w, 31));
+      if (lane == 0) fz_publish(tile == 0 ? &z.incl[0] : &z.agg[tile], agg);
+      uint4 pre = make_uint4(0, 0, 0, 0);
+      if (tile > 0) {
+        // (64 predecessors per round, two per lane, measured slower: 1.89 against 1.19 ms per 2^22 reads -- the wait
+        // is for the NEAREST predecessors' own totals, and a wider window only adds words to poll)
+        int32_t j = (int32_t)tile - 1 - (int32_t)lane;
+        for (;;) {
+          uint4 val = make_uint4(0, 0, 0, 0);
+          uint32_t st;  // 2: totals up to and including tile j, 1: tile j's own totals, 0: nothing yet
+          do {
+            st = 2u;
+            if (j >= 0) st = fz_read(&z.incl[j], &val) ? 2u : (fz_read(&z.agg[j], &val) ? 1u : 0u);
+          } while (__any_sync(0xFFFFFFFFu, st == 0u));
+          const uint32_t done = __ballot_sync(0xFFFFFFFFu, st == 2u);  // j < 0 counts: everything before tile 0 is 0
+          const uint32_t first = done ? (uint32_t)__ffs(done) - 1u : 32u;
+          if (lane > first) val = make_uint4(0, 0, 0, 0);
+#pragma unroll
+          for (int dd = 16; dd > 0; dd >>= 1) {
+            val.x += __shfl_xor_sync(0xFFFFFFFFu, val.x, dd);
+            val.y += __shfl_xor_sync(0xFFFFFFFFu, val.y, dd);
+            val.z += __shfl_xor_sync(0xFFFFFFFFu, val.z, dd);
+            val.w += __shfl_xor_sync(0xFFFFFFFFu, val.w, dd);
+          }
+          pre = add4(pre, val);
+          if (done) break;
+          j -= 32;
+        }
+        if (lane == 0) fz_publish(&z.incl[tile], add4(pre, agg));
+      }
+      // ---- E: keys of the tile's reads in their streams, source offsets, output offsets / source indices
+      uint4 run = make_uint4(pre.x + inc.x - sum.x, pre.y + inc.y - sum.y, pre.z + inc.z - sum.z, pre.w + inc.w - sum.w);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const uint32_t r = 4u * lane + k;
+        if (r <= nt) {
+          h.ct.key[0][r] = run.x;
+          h.ct.key[1][r] = run.y;
+        }
+        if (r < nt) {
+          h.ct.soff[r] = h.sidx[r] + h.start[r] - S0a + CT_PAD;
+          if (h.pass[r]) {
+            b.out_src[run.z] = i0 + r;
+            b.out_idx[run.z] = run.x;
+          } else {
+            z.fail_src[run.w] = i0 + r;
+            z.fail_idx[run.w] = run.y;
           }
         }
+        run = add4(run, v[k]);
+      }
+      if (lane == 31 && nt == 4u * 32u) {  // a full tile: the end of both spans lies behind the last lane's reads
+        h.ct.key[0][nt] = run.x;
+        h.ct.key[1][nt] = run.y;
+      }
+      if (lane == 0) h.prefix = pre;
+    }
+    __syncthreads();
+    // chunk -> read map of both spans
+    const uint32_t D0p = h.ct.key[0][0], D1p = h.ct.key[0][nt], D0f = h.ct.key[1][0];
+    const uint32_t mo_f = ((D1p + 15u) >> 4) - (D0p >> 4) + 1u;
+    for (uint32_t r = tid; r < nt; r += 256u) {
+      const uint32_t st = h.pass[r] ? 0u : 1u;
+      const uint32_t k0 = h.ct.key[st][r], k1 = h.ct.key[st][r + 1u], D0s = st ? D0f : D0p;
+      if (k1 > k0) {
+        const uint32_t cb = D0s >> 4;
+        const uint32_t cf = k0 == D0s ? cb : (k0 + 15u) >> 4, cl = (k1 - 1u) >> 4;
+        uint8_t *mp = rmap + (st ? mo_f : 0u) - cb;
+        for (uint32_t c = cf; c <= cl; ++c) mp[c] = (uint8_t)r;
+      }
+    }
+    __syncthreads();
+    // ---- F: the two output spans
+    uint8_t *const oseq[2] = {b.out_seq, z.fail_seq}, *const oqual[2] = {b.out_qual, z.fail_qual};
+    ct_emit(h.ct, rmap, mo_f, sseq, squal, nt, oseq, oqual);
+  }
+  unsigned long long *C = a.ctr;
+  n_pass = group_sum<32>(n_pass);
+  n_fail = group_sum<32>(n_fail);
+  n_edit = group_sum<32>(n_edit);
+  if (lane == 0) {
+    if (n_pass) atomicAdd(&C[HPGQ_S_NUM_PASSED], (unsigned long long)n_pass);
+    if (n_fail) atomicAdd(&C[HPGQ_S_NUM_FAILED], (unsigned long long)n_fail);
+    if (n_edit) atomicAdd(&C[HPGQ_S_NUM_EDITED], (unsigned long long)n_edit);
+  }
+}
+
+// The failed reads' bytes, offsets and source indices move behind the passed reads; totals for the host.
+__global__ void __launch_bounds__(256) hq_fz_finish(hq_kargs a, hq_compact_bufs b, fz_bufs z) {
+  uint4 tot = make_uint4(0, 0, 0, 0);
+  if (z.n_tiles) (void)fz_read(&z.incl[z.n_tiles - 1u], &tot);
+  const uint32_t gtid = blockIdx.x * blockDim.x + threadIdx.x, gstride = gridDim.x * blockDim.x;
+  const uint32_t D0 = tot.x, D1 = tot.x + tot.y;
+  for (uint32_t c = (D0 >> 4) + gtid; c < ((D1 + 15u) >> 4); c += gstride) {
+    const uint32_t dc = c << 4, d0 = max(dc, D0), d1 = min(dc + 16u, D1);
+    const uint32_t x = dc - D0;  // side-buffer byte that lands on byte 0 of the chunk (mod 2^32: may be "negative")
+    const uint32_t xa = x & ~15u;
+    uint4 As = make_uint4(0, 0, 0, 0), Aq = As, Bs = As, Bq = As;
+    if (dc >= D0) {
+      As = *reinterpret_cast<const uint4 *>(z.fail_seq + xa);
+      Aq = *reinterpret_cast<const uint4 *>(z.fail_qual + xa);
+    }
+    if (xa + 16u < tot.y + 16u || dc < D0) {  // the B half exists (the side buffers are padded by 64 bytes)
+      Bs = *reinterpret_cast<const uint4 *>(z.fail_seq + (dc >= D0 ? xa + 16u : 0u));
+      Bq = *reinterpret_cast<const uint4 *>(z.fail_qual + (dc >= D0 ? xa + 16u : 0u));
+    }
+    const uint4 vs = shift_sel(As, Bs, x & 15u), vq = shift_sel(Aq, Bq, x & 15u);
+    if (d1 - d0 == 16u) {
+      *reinterpret_cast<uint4 *>(b.out_seq + dc) = vs;
+      *reinterpret_cast<uint4 *>(b.out_qual + dc) = vq;
+    } else {
+      const uint32_t ws[4] = {vs.x, vs.y, vs.z, vs.w}, wq[4] = {vq.x, vq.y, vq.z, vq.w};
+      for (uint32_t t = d0 - dc; t < d1 - dc; ++t) {
+        b.out_seq[dc + t] = (uint8_t)(ws[t >> 2] >> (8u * (t & 3u)));
+        b.out_qual[dc + t] = (uint8_t)(wq[t >> 2] >> (8u * (t & 3u)));
       }
     }
   }
-  if (blockIdx.x == 0 && tid == 0) b.out_idx[n] = tot.x + tot.y;
+  for (uint32_t j = gtid; j < tot.w; j += gstride) {
+    b.out_idx[tot.z + j] = tot.x + z.fail_idx[j];
+    b.out_src[tot.z + j] = z.fail_src[j];
+  }
+  if (gtid == 0) {
+    b.out_idx[a.n_reads] = D1;
+    b.totals[0] = tot.z;
+    b.totals[1] = tot.w;
+    b.totals[2] = tot.x;
+    b.totals[3] = tot.y;
+  }
 }
 
 // Order-sensitive 64-bit checksum of a slot's compacted output (bench.py compares it across GPU counts, tests with
@@ -407,6 +860,80 @@ cudaError_t hq_launch_checksum(const hq_compact_bufs &b, uint32_t n, unsigned lo
   cudaError_t e = cudaMemsetAsync(d_out, 0, 8, st);
   if (e != cudaSuccess) return e;
   hq_checksum_kernel<<<148 * 8, 256, 0, st>>>(b, n, d_out);
+  ++*launches;
+  return cudaGetLastError();
+}
+
+namespace {
+uint32_t fz_rpt(uint32_t max_len) {
+  uint32_t rpt = CT_SPAN / (max_len ? max_len : 1u);
+  return rpt > CT_RPT ? CT_RPT : rpt;
+}
+}  // namespace
+
+bool hq_fz_supports(uint32_t work, uint32_t max_len, uint32_t n_reads, const hq_compact_bufs &b) {
+  if (!(work & HPGQ_WORK_COMPACT) || (work & (HPGQ_WORK_STATS | HPGQ_WORK_KMERS | HPGQ_WORK_CHAOS))) return false;
+  if (!(work & (HPGQ_WORK_EDIT | HPGQ_WORK_FILTER))) return false;
+  if (max_len == 0 || max_len + 15u > 32u * RG_LB || !b.fz_status) return false;  // reads held in registers by <= 32 lanes
+  const uint32_t rpt = fz_rpt(max_len);
+  return rpt >= 16u && (n_reads + rpt - 1u) / rpt <= b.fz_tiles_cap;
+}
+
+cudaError_t hq_launch_fz(const hq_kargs &a, const hq_compact_bufs &b, uint32_t max_len, int sm_count, cudaStream_t st,
+                         uint64_t *launches) {
+  fz_bufs z;
+  z.agg = reinterpret_cast<fz_rec *>(b.fz_agg);
+  z.incl = reinterpret_cast<fz_rec *>(b.fz_incl);
+  z.status = b.fz_status;
+  z.fail_seq = b.fail_seq;
+  z.fail_qual = b.fail_qual;
+  z.fail_idx = b.fail_idx;
+  z.fail_src = b.fail_src;
+  z.rpt = fz_rpt(max_len);
+  z.cap = ((z.rpt * max_len + 15u) & ~15u) + 64u;
+  z.n_tiles = (a.n_reads + z.rpt - 1u) / z.rpt;
+  cudaError_t e = cudaMemsetAsync(z.status, 0, 4, st);
+  if (e == cudaSuccess) e = cudaMemsetAsync(z.agg, 0, (size_t)z.n_tiles * sizeof(fz_rec), st);
+  if (e == cudaSuccess) e = cudaMemsetAsync(z.incl, 0, (size_t)z.n_tiles * sizeof(fz_rec), st);
+  if (e != cudaSuccess) return e;
+  const uint32_t smem = (((uint32_t)sizeof(fz_hdr) + 15u) & ~15u) + ct_rmap_bytes(z.cap) + 2u * z.cap;
+  const uint32_t span = max_len + 15u;
+  int G = span <= 4u * RG_LB ? 4 : span <= 8u * RG_LB ? 8 : span <= 16u * RG_LB ? 16 : 32;
+  const bool ooq = (a.work & HPGQ_WORK_FILTER) != 0 && a.max_ooq < 32 * RG_LB;
+  // the word-frame decision (fz_decide_fast) takes batches without filter windows or an out-of-quality limit, trim
+  // windows of <= 255 bases and reads of <= 4 K G - 3 bases (K = 5); HPGQ_FZ_SLOW keeps the register code (tests)
+  const bool windows = (a.work & HPGQ_WORK_FILTER) != 0 && (a.f_ll > 0 || a.f_rl > 0);
+  bool fast = !ooq && !windows && a.e_ll <= 255 && a.e_rl <= 255 && max_len <= 20u * 32u - 3u && !getenv("HPGQ_FZ_SLOW");
+  if (fast) G = max_len <= 77u ? 4 : max_len <= 157u ? 8 : max_len <= 317u ? 16 : 32;
+  if (a.n_reads) {
+#define HQ_FZ(KK, GG, OO, FF)                                                                                     \
+  do {                                                                                                           \
+    e = cudaFuncSetAttribute(hq_fz_kernel<KK, GG, OO, FF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+    int per_sm = 1;                                                                                              \
+    if (e == cudaSuccess)                                                                                        \
+      e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, hq_fz_kernel<KK, GG, OO, FF>, 256, smem);       \
+    if (e != cudaSuccess) return e;                                                                              \
+    uint32_t grid = (uint32_t)sm_count * (uint32_t)(per_sm > 0 ? per_sm : 1);                                    \
+    if (grid > z.n_tiles) grid = z.n_tiles;                                                                      \
+    hq_fz_kernel<KK, GG, OO, FF><<<grid, 256, smem, st>>>(a, b, z);                                              \
+  } while (0)
+#define HQ_FZ_G(GG)                              \
+  do {                                           \
+    if (fast) HQ_FZ(5, GG, false, true);         \
+    else if (ooq) HQ_FZ(1, GG, true, false);     \
+    else HQ_FZ(1, GG, false, false);             \
+  } while (0)
+    switch (G) {
+      case 4: HQ_FZ_G(4); break;
+      case 8: HQ_FZ_G(8); break;
+      case 16: HQ_FZ_G(16); break;
+      default: HQ_FZ_G(32); break;
+    }
+#undef HQ_FZ_G
+#undef HQ_FZ
+    ++*launches;
+  }
+  hq_fz_finish<<<sm_count * 4, 256, 0, st>>>(a, b, z);
   ++*launches;
   return cudaGetLastError();
 }

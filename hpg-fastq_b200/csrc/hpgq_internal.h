@@ -65,7 +65,17 @@ struct hq_compact_bufs {
   uint8_t *out_seq, *out_qual;
   uint32_t *out_idx, *out_src; // n+1 / n
   uint32_t *totals;            // [0]=n_passed [1]=n_failed [2]=passed_bytes [3]=failed_bytes (device)
+  // one-pass (fused) path: per-tile look-back records and the side buffers of the failed stream
+  uint4 *fz_agg, *fz_incl;
+  uint32_t *fz_status;         // fz_tiles_cap + 1 words (the last one is the tile ticket)
+  uint32_t fz_tiles_cap;
+  uint8_t *fail_seq, *fail_qual;
+  uint32_t *fail_idx, *fail_src;
 };
+// decisions (trim, filter) and compaction in one pass over the batch; false = this batch needs the two-pass path
+bool hq_fz_supports(uint32_t work, uint32_t max_len, uint32_t n_reads, const hq_compact_bufs &b);
+cudaError_t hq_launch_fz(const hq_kargs &a, const hq_compact_bufs &b, uint32_t max_len, int sm_count, cudaStream_t st,
+                         uint64_t *launches);
 cudaError_t hq_launch_compact(const hq_kargs &a, const hq_compact_bufs &b, uint32_t mean_len, uint32_t max_len,
                               cudaStream_t st, uint64_t *launches);
 

@@ -172,7 +172,12 @@ def test_device_resident_generator_matches_host(q, ob):
         ctx.free_batch(b)
 
 
-def test_edit_trim_filter_compact(q, ob):
+@pytest.mark.parametrize("no_fuse", [None, 2, 1], ids=["one_pass", "one_pass_register_decisions", "two_pass"])
+def test_edit_trim_filter_compact(q, ob, no_fuse, monkeypatch):
+    """Both compaction paths: the one-pass kernel (decisions + look-back + output from the staged tile) and the
+    two-pass path (decision kernel, scan, gather; HPGQ_NO_FUSE)."""
+    if no_fuse:
+        monkeypatch.setenv("HPGQ_NO_FUSE" if no_fuse == 1 else "HPGQ_FZ_SLOW", "1")
     seq, qual, idx = pack(EDIT_READS)
     par = q.make_params(q.WORK_EDIT | q.WORK_FILTER | q.WORK_COMPACT, edit=EDIT_OPTS, filter=dict(min_read_length=3))
     _, res, _, emask, etrim = check(q, ob, par, seq, qual, idx, 8)
@@ -265,9 +270,13 @@ def test_long_reads_group_and_position_kernels(q, ob):
     check(q, ob, q.make_params(q.WORK_STATS | q.WORK_FILTER, filter=dict(min_read_length=100, max_N=3)), seq, qual, idx, 9024)
 
 
+@pytest.mark.parametrize("no_fuse", [None, 2, 1], ids=["one_pass", "one_pass_register_decisions", "two_pass"])
 @pytest.mark.parametrize("lmax", [20, 60, 110, 300, 700, 2500])
-def test_edit_group_kernel_all_lane_widths(q, ob, lmax):
-    """EDIT + FILTER (+ filter windows) on ragged reads: every lanes-per-read instantiation of the group kernel."""
+def test_edit_group_kernel_all_lane_widths(q, ob, lmax, no_fuse, monkeypatch):
+    """EDIT + FILTER (+ filter windows) on ragged reads: every lanes-per-read instantiation of the group kernel and
+    of the one-pass kernel (reads of 2500 bp take the two-pass path either way)."""
+    if no_fuse:
+        monkeypatch.setenv("HPGQ_NO_FUSE" if no_fuse == 1 else "HPGQ_FZ_SLOW", "1")
     rng = np.random.default_rng(lmax)
     seq, qual, idx = rand_batch(rng, 6000, 0, lmax, p_n=0.03)
     qual = rng.integers(35, 74, size=len(qual)).astype(np.uint8)
@@ -511,3 +520,43 @@ def test_chaos_game_exact_inside_a_large_batch(q, ob):
     par = q.make_params(q.WORK_KMERS | q.WORK_CHAOS, k2=11, cg_k=10)
     got, *_ = check(q, ob, par, seq, qual, idx, 160, kmers=True, k2=11, cg_k=10)
     assert got[q.S["CG_FIXED_READS"]] >= 400
+
+
+@pytest.mark.parametrize("L,n", [(150, 300000), (36, 500000), (1000, 40000)])
+def test_one_pass_compaction_many_tiles(q, ob, L, n):
+    """Thousands of tiles through the decoupled look-back: filter-only, edit-only and edit + filter, most reads failing
+    (a large failed stream through the side buffer), every read failing, every read passing."""
+    seq, qual, idx = q.synth_host(q.synth_cfg(L, short_pct=4, short_min=max(L // 4, 1)), 5, n)
+    edit = dict(left_length=10, min_left_quality=30, right_length=12, min_right_quality=22)
+    cases = [(q.WORK_EDIT | q.WORK_FILTER | q.WORK_COMPACT, dict(min_read_length=L // 2, min_read_quality=20, max_N=5)),
+             (q.WORK_FILTER | q.WORK_COMPACT, dict(min_read_quality=36)),          # most reads fail
+             (q.WORK_FILTER | q.WORK_COMPACT, dict(min_read_quality=60)),          # all fail
+             (q.WORK_EDIT | q.WORK_COMPACT, None),                                 # all pass, trimmed
+             (q.WORK_FILTER | q.WORK_COMPACT, dict(min_read_quality=25, max_out_of_quality=L // 3))]
+    for work, flt in cases:
+        par = q.make_params(work, edit=edit, filter=flt)
+        _, res, _, emask, etrim = check(q, ob, par, seq, qual, idx, 1024)
+        cp = ob.compact(seq, qual, idx, emask if work & q.WORK_FILTER else None, etrim if work & q.WORK_EDIT else None)
+        assert res["n_passed"] == cp["n_passed"] and res["passed_bytes"] == cp["passed_bytes"]
+        assert res["failed_bytes"] == cp["failed_bytes"]
+        for k in ("out_idx", "out_src", "out_seq", "out_qual"):
+            assert np.array_equal(res[k], cp[k]), k
+
+
+@pytest.mark.parametrize("lmax", [30, 75, 150, 310, 630])
+def test_one_pass_word_frame_decisions_on_ragged_reads(q, ob, lmax):
+    """The word-frame decision of the one-pass kernel (no filter windows, no out-of-quality limit) in each of its lane
+    widths, on reads of every length from 0 up: reads shorter than the two trim windows fall back to the register
+    code inside the same warp iteration."""
+    rng = np.random.default_rng(1000 + lmax)
+    seq, qual, idx = rand_batch(rng, 20000, 0, lmax, p_n=0.04)
+    qual = rng.integers(35, 74, size=len(qual)).astype(np.uint8)
+    for edit, flt in ((dict(left_length=9, min_left_quality=22, max_left_quality=30, right_length=13, min_right_quality=19,
+                            max_right_quality=28), dict(min_read_length=4, min_read_quality=18, max_read_quality=24, max_N=3)),
+                      (dict(left_length=255, min_left_quality=21, right_length=3, min_right_quality=23), dict(max_N=1))):
+        par = q.make_params(q.WORK_EDIT | q.WORK_FILTER | q.WORK_COMPACT, edit=edit, filter=flt)
+        _, res, _, emask, etrim = check(q, ob, par, seq, qual, idx, lmax + 8)
+        assert 0 < int(emask.sum()) < len(emask)
+        cp = ob.compact(seq, qual, idx, emask, etrim)
+        for k in ("out_idx", "out_src", "out_seq", "out_qual"):
+            assert np.array_equal(res[k], cp[k]), k
