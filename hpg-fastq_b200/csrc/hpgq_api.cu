@@ -76,6 +76,7 @@ struct hpgq_ctx {
   hpgq_layout_t lay = {};
   unsigned long long *d_ctr = nullptr;
   unsigned long long *d_cgpack = nullptr;  // packed chaos-game shadow table, always all-zero between batches
+  unsigned long long *d_kcpack = nullptr;  // packed k2-mer + chaos-game table (both reserved, k2 >= cg_k), all-zero between batches
   hpgq_slot slot[HPGQ_MAX_SLOTS];
   uint64_t launches = 0;
   uint64_t batches = 0;
@@ -203,6 +204,7 @@ extern "C" int hpgq_ctx_destroy(hpgq_ctx_t *ctx) {
   for (int i = 0; i < HPGQ_MAX_SLOTS; ++i) slot_free(ctx->slot[i]);
   cudaFree(ctx->d_ctr);
   cudaFree(ctx->d_cgpack);
+  cudaFree(ctx->d_kcpack);
   delete ctx;
   return HPGQ_OK;
 }
@@ -238,6 +240,10 @@ extern "C" int hpgq_ctx_create(int device, const hpgq_limits_t *lim, hpgq_ctx_t 
   if (e == cudaSuccess && lim->cg_k) {
     e = cudaMalloc(&c->d_cgpack, (8ull << (2 * lim->cg_k)));
     if (e == cudaSuccess) e = cudaMemset(c->d_cgpack, 0, (8ull << (2 * lim->cg_k)));
+    if (e == cudaSuccess && lim->kmers && lim->k2 >= lim->cg_k) {
+      e = cudaMalloc(&c->d_kcpack, (8ull << (2 * lim->k2)));
+      if (e == cudaSuccess) e = cudaMemset(c->d_kcpack, 0, (8ull << (2 * lim->k2)));
+    }
   }
   const size_t nb = (size_t)lim->max_bytes_per_batch + 64, nr = (size_t)lim->max_reads_per_batch;
   for (uint32_t i = 0; i < c->lim.n_slots && e == cudaSuccess; ++i) {

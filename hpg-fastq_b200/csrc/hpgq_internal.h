@@ -29,6 +29,7 @@ struct hq_kargs {
   uint32_t o_len_hist, o_sumq, o_qual_hist, o_gc_hist, o_accq, o_A, o_C, o_G, o_T, o_N;
   uint64_t o_k5, o_k5pos, o_k2, o_cg_seq, o_cg_q;
   unsigned long long *cg_pack; // packed chaos-game shadow table (count << 38 | quality sum), NULL = not used
+  unsigned long long *kc_pack; // packed k2-mer + chaos-game table (4^k2 cells, same packing), NULL = not used
   // per-read outputs
   uint8_t *mask;     // may be NULL
   hpgq_trim_t *trim; // may be NULL

@@ -157,6 +157,39 @@ __global__ void __launch_bounds__(256) hq_cg_unpack_kernel(hq_kargs a, uint32_t 
   }
 }
 
+// Packed k2-mer / chaos-game table -> K2, CG_SEQ, CG_Q.  Cell c (a k2-mer, first base most significant) holds
+// count << 38 | quality sum of the words that ended with it; the chaos-game cell of those words is
+// co_x = sum xbit(base_i) 2^i, co_y = sum ybit(base_i) 2^i over the last cg_k bases, oldest = bit 0
+// (old/chaos_game.c:200-228: A, T move x up; G, T move y up).
+__global__ void __launch_bounds__(256) hq_kc_unpack_kernel(hq_kargs a, uint32_t cells) {
+  // a thread owns one chaos-game cell = the 4^(k2 - cg_k) k2-mers that end with the same cg_k bases: no atomics
+  unsigned long long *C = a.ctr;
+  const int ck = a.cg_k;
+  const uint32_t low = 1u << (2 * ck), tops = cells >> (2 * ck);
+  for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < low; c += gridDim.x * blockDim.x) {
+    unsigned long long cnt = 0, qs = 0;
+    for (uint32_t t = 0; t < tops; ++t) {
+      const uint32_t code = t * low + c;
+      const unsigned long long v = a.kc_pack[code];
+      if (!v) continue;
+      a.kc_pack[code] = 0ull;
+      C[a.o_k2 + code] += v >> 38;
+      cnt += v >> 38;
+      qs += v & ((1ull << 38) - 1ull);
+    }
+    if (!cnt) continue;
+    uint32_t ix = 0, iy = 0;
+    for (int i = 0; i < ck; ++i) {
+      const uint32_t b = (c >> (2 * (ck - 1 - i))) & 3u;
+      ix |= (uint32_t)(b == 0u || b == 3u) << i;
+      iy |= (b >> 1) << i;
+    }
+    const uint64_t cell = ((uint64_t)ix << ck) + iy;
+    C[a.o_cg_seq + cell] += cnt;
+    C[a.o_cg_q + cell] += qs;
+  }
+}
+
 __device__ __forceinline__ int base2(uint32_t c) {
   return c == 'A' ? 0 : c == 'C' ? 1 : c == 'G' ? 2 : c == 'T' ? 3 : -1;
 }
@@ -176,6 +209,7 @@ __global__ void __launch_bounds__(256) hq_kmers_cg_kernel(hq_kargs a) {
   const uint32_t k2mask = k2 > 0 ? ((k2 >= 16) ? 0xFFFFFFFFu : ((1u << (2 * k2)) - 1u)) : 0u;
   unsigned long long *C = a.ctr;
   unsigned long long words = 0, longruns = 0;
+  const bool merged = a.kc_pack != nullptr && do_k && do_cg && k2 >= ck;
 
   for (uint32_t r0 = warp * NG; r0 < a.n_reads; r0 += nwarps * NG) {  // warp-uniform trip count (ballots below)
     const uint32_t r = r0 + giw;
@@ -236,16 +270,27 @@ __global__ void __launch_bounds__(256) hq_kmers_cg_kernel(hq_kargs a) {
         }
         if (j < cb) continue;
         if (b >= 0) {
-          if (kmers_here) {
+          // One 64-bit RED per base when k-mers and chaos game run together: the chaos-game cell of a word is a bit
+          // permutation of the low 2 cg_k bits of the k2-mer that ends at the same base, so the k2-mer count and the
+          // word's quality sum travel as (1 << 38 | qsum) into ONE packed table indexed by the k2-mer;
+          // hq_kc_unpack_kernel splits it into K2, CG_SEQ and CG_Q.  The two tables were 2 REDs per base, and the
+          // kernel runs at the L2 atomic rate (~189 G RED/s).
+          const uint32_t qval = accq - (uint32_t)(a.cg_base_quality * ck);
+          const bool kev = kmers_here && k2 > 0 && valid >= (uint32_t)k2;
+          const bool cev = do_cg && !other && cnt >= (uint32_t)ck;
+          if (merged && kev && cev && qval < 4096u) {
+            atomicAdd(&a.kc_pack[code & k2mask], (1ull << 38) | (unsigned long long)qval);
+            words++;
+          } else {
             // 5-mer x start position: hq_k5pos_kernel (shared-memory slices); the 5-mer totals are the row sums of
             // that table, derived at download (hpgq_counters_finalize_host)
-            if (k2 > 0 && valid >= (uint32_t)k2) atomicAdd(&C[a.o_k2 + (code & k2mask)], 1ull);
-          }
-          if (do_cg && !other) {
-            if (cnt >= (uint32_t)ck) {
-              cg_add(a, ((uint64_t)ix << ck) + iy, accq - (uint32_t)(a.cg_base_quality * ck));
+            if (kev) atomicAdd(&C[a.o_k2 + (code & k2mask)], 1ull);
+            if (cev) {
+              cg_add(a, ((uint64_t)ix << ck) + iy, qval);
               words++;
             }
+          }
+          if (do_cg && !other) {
             if (run_x == 21u || run_y == 21u) {
               longruns++;
               if (a.cgflag) a.cgflag[r] = 1;
@@ -622,6 +667,12 @@ cudaError_t hq_launch_kmers_cg(const hq_kargs &a0, uint32_t max_len_in_batch, cu
     if (cg && a.cg_pack) {
       const uint32_t cells = 1u << (2 * a.cg_k);
       hq_cg_unpack_kernel<<<(cells + 1023u) / 1024u < 592u ? (cells + 1023u) / 1024u : 592u, 256, 0, st>>>(a, cells);
+      ++*launches;
+    }
+    if (cg && a.kc_pack && (a.work & HPGQ_WORK_KMERS) && a.k2 >= a.cg_k) {
+      const uint32_t cells = 1u << (2 * a.k2);
+      const uint32_t own = 1u << (2 * a.cg_k);
+      hq_kc_unpack_kernel<<<(own + 255u) / 256u < 2368u ? (own + 255u) / 256u : 2368u, 256, 0, st>>>(a, cells);
       ++*launches;
     }
   }

@@ -560,3 +560,32 @@ def test_one_pass_word_frame_decisions_on_ragged_reads(q, ob, lmax):
         cp = ob.compact(seq, qual, idx, emask, etrim)
         for k in ("out_idx", "out_src", "out_seq", "out_qual"):
             assert np.array_equal(res[k], cp[k]), k
+
+
+@pytest.mark.parametrize("k2,ck", [(11, 10), (7, 7), (9, 3), (3, 5), (13, 12)])
+def test_kmers_and_chaos_game_single_reduction_path(q, ob, k2, ck, monkeypatch):
+    """k-mers + chaos game without a filter: one packed reduction per base, split into K2 / CG_SEQ / CG_Q afterwards
+    (k2 >= cg_k; (3, 5) keeps the two-table path).  Ns, long axis runs, low qualities below the base quality (values
+    that do not fit the packed field), two batches accumulated, and the same through HPGQ_NO_KCPACK."""
+    rng = np.random.default_rng(k2 * 16 + ck)
+    seq, qual, idx = rand_batch(rng, 20000, 0, 180, p_n=0.02)
+    qual = rng.integers(33, 74, size=len(qual)).astype(np.uint8)
+    qual[rng.integers(0, len(qual), 500)] = 20  # below the base quality: the word's sum can wrap
+    seq = seq.copy()
+    o = int(idx[100])
+    seq[o:o + 60] = ord("T")
+    par = q.make_params(q.WORK_KMERS | q.WORK_CHAOS, k2=k2, cg_k=ck)
+    for env in (None, "1"):
+        if env:
+            monkeypatch.setenv("HPGQ_NO_KCPACK", env)
+        with q.Ctx(0, max_reads=20000, max_bytes=int(idx[-1]), max_read_len=192, kmers=True, k2=k2, cg_k=ck) as ctx:
+            ctx.set_params(par)
+            for _ in range(2):
+                ctx.submit(seq, qual, idx, 0)
+                ctx.wait(0)
+            got = ctx.counters()
+            lay = ctx.layout
+        exp, _, _ = ob.process_batch(par, lay, seq, qual, idx, finalize=False)
+        exp, _, _ = ob.process_batch(par, lay, seq, qual, idx, counters=exp)
+        msg = diff_report(q, lay, got, exp)
+        assert not msg, msg
