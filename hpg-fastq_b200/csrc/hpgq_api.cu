@@ -64,6 +64,8 @@ struct hpgq_slot {
   hq_parse_bufs pb = {};
   uint32_t *h_pinfo = nullptr;  // pinned copy of pb.info
   bool text_batch = false;
+  bool text_pending = false;         // a chunk is parsed / being parsed, hpgq_batch_text_launch not called yet
+  cudaEvent_t ev_parse = nullptr;    // end of the parse chain + info block copy
   uint8_t *d_otext = nullptr, *h_otext = nullptr;  // FASTQ text of the compacted output (hpgq_batch_wait_text)
   uint64_t otext_cap = 0;
 };
@@ -191,6 +193,7 @@ static void slot_free(hpgq_slot &s) {
   cudaFree(s.d_otext); cudaFreeHost(s.h_otext);
   cudaFree(s.pb.tile_cnt); cudaFree(s.pb.cta_sum); cudaFree(s.pb.nl); cudaFree(s.pb.info);
   cudaFree(s.pb.seq_off); cudaFree(s.pb.qual_off); cudaFree(s.pb.hdr_off); cudaFree(s.pb.hdr_len);
+  if (s.ev_parse) cudaEventDestroy(s.ev_parse);
   if (s.ev0) cudaEventDestroy(s.ev0);
   if (s.ev1) cudaEventDestroy(s.ev1);
   if (s.stream) cudaStreamDestroy(s.stream);

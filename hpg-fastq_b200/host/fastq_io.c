@@ -258,6 +258,10 @@ void hq_reader_advance(hq_reader_t *r, uint64_t bytes, uint64_t records) {
   r->record += records;
 }
 
+int hq_reader_fd(const hq_reader_t *r) { return r->fd; }
+
+void hq_reader_rewind(hq_reader_t *r, uint64_t pos) { r->pos = pos; }
+
 /* ------------------------------------------------------------------ writer */
 struct hq_writer {
   int fd;

@@ -108,6 +108,8 @@ const char *hq_reader_error(const hq_reader_t *r);
  * does not move until hq_reader_advance. */
 int hq_reader_peek_text(const hq_reader_t *r, uint64_t max_bytes, uint64_t *off, uint64_t *len);
 void hq_reader_advance(hq_reader_t *r, uint64_t bytes, uint64_t records);
+int hq_reader_fd(const hq_reader_t *r);                 /* the open input, for hpgq_batch_submit_text_fd */
+void hq_reader_rewind(hq_reader_t *r, uint64_t pos);    /* back to a chunk the device parser handed back */
 
 /* ------------------------------------------------------------------ FASTQ writer */
 typedef struct hq_writer hq_writer_t;

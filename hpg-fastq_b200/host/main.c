@@ -149,6 +149,10 @@ typedef struct run {
   uint64_t n_text_batches, n_host_batches;
   wqueue_t wq;
   uint64_t wq_id[HQ_MAX_GPUS][HQ_SLOTS]; /* last writer job that reads the slot's text buffer */
+  /* the text chunk whose parse is in flight: its QC kernels are launched one chunk later (resolve_pending), so that
+   * the next chunk is staged and copied while the device parses this one */
+  int pend, pend_g, pend_s;
+  uint64_t pend_off, pend_len;
 } run_t;
 
 /* the pinned SoA arrays are only needed by the host reader: with the device parser they are allocated when (if)
@@ -248,37 +252,110 @@ static int consume(run_t *r, int g, int s) {
   return 0;
 }
 
+/* Launches the QC kernels of the pending text chunk.  0 = done; 1 = fatal; 2 = the device parser handed the chunk
+ * back (the reader stands at its start again, and either the chunk budget was halved or the host reader takes over). */
+static int resolve_pending(run_t *r) {
+  if (!r->pend) return 0;
+  r->pend = 0;
+  const int g = r->pend_g, s = r->pend_s;
+  hpgq_text_info_t info;
+  int rc = hpgq_batch_text_launch(r->ctx[g], s, &info);
+  if (rc) return die_hpgq("hpgq_batch_text_launch", rc);
+  if (info.status == 0) {
+    r->hb[g][s].n_reads = info.n_reads;
+    r->hb[g][s].max_len = info.max_len;
+    hq_reader_advance(r->reader, 0, info.n_reads);
+    r->busy[g][s] = 1;
+    r->is_text[g][s] = 1;
+    r->n_text_batches++;
+    return 0;
+  }
+  hq_reader_rewind(r->reader, r->pend_off);
+  if (info.status == HPGQ_TEXT_TOO_MANY && r->text_budget > (1u << 16)) {
+    r->text_budget /= 2; /* shorter reads than the sizing assumed: same chunk again, smaller */
+    return 2;
+  }
+  /* blank lines, a malformed record: the host reader takes over (and owns the messages) */
+  r->device_parse = 0;
+  logf_("INFO", "device FASTQ parser handed the input back to the host reader");
+  return 2;
+}
+
 static int run_pipeline(run_t *r) {
   const int N = r->n_gpus;
   uint64_t b = 0;
   for (;; b++) {
     const int g = (int)(b % (uint64_t)N), s = (int)((b / (uint64_t)N) % HQ_SLOTS);
+    if (r->pend && r->pend_g == g && r->pend_s == s) { /* a single slot in all: nothing to overlap */
+      const int st = resolve_pending(r);
+      if (st == 1) return 1;
+      if (st == 2) {
+        b--;
+        continue;
+      }
+    }
     if (r->busy[g][s] && consume(r, g, s)) return 1;
     hq_host_batch_t *hb = &r->hb[g][s];
     if (r->device_parse) {
       uint64_t off = 0, len = 0;
       const int pk = hq_reader_peek_text(r->reader, r->text_budget, &off, &len);
-      if (pk == 0) break;
-      if (pk > 0) {
-        hpgq_text_info_t info;
-        int rc = hpgq_batch_submit_text(r->ctx[g], hq_reader_data(r->reader) + off, len, s, &info);
-        if (rc) return die_hpgq("hpgq_batch_submit_text", rc);
-        if (info.status == 0) {
-          hb->n_reads = info.n_reads;
-          hb->max_len = info.max_len;
-          hq_reader_advance(r->reader, len, info.n_reads);
-          r->busy[g][s] = 1;
-          r->is_text[g][s] = 1;
-          r->n_text_batches++;
+      if (pk == 0) {
+        const int st = resolve_pending(r);
+        if (st == 1) return 1;
+        if (st == 2) {
+          b--;
           continue;
         }
-        if (info.status == HPGQ_TEXT_TOO_MANY && r->text_budget > (1u << 16)) {
-          r->text_budget /= 2; /* shorter reads than the sizing assumed: same batch again, smaller chunk */
+        break;
+      }
+      if (pk > 0) {
+        /* chunk b is read (pread threads, pinned staging), copied and parsed while chunk b - 1 is still being parsed;
+         * only then are the kernels of chunk b - 1 launched */
+        int rc;
+        if (getenv("HPGQ_TEXT_SYNC")) { /* developer A/B: the one-call form (copy from the mapping, parse awaited at once) */
+          hpgq_text_info_t info;
+          rc = hpgq_batch_submit_text(r->ctx[g], hq_reader_data(r->reader) + off, len, s, &info);
+          if (rc) return die_hpgq("hpgq_batch_submit_text", rc);
+          if (info.status == 0) {
+            hb->n_reads = info.n_reads;
+            hb->max_len = info.max_len;
+            hq_reader_advance(r->reader, len, info.n_reads);
+            r->busy[g][s] = 1;
+            r->is_text[g][s] = 1;
+            r->n_text_batches++;
+            continue;
+          }
+          r->device_parse = 0;
+          b--;
+          continue;
+        }
+        rc = hpgq_batch_submit_text_fd(r->ctx[g], hq_reader_fd(r->reader), off, len, s);
+        if (rc) return die_hpgq("hpgq_batch_submit_text_fd", rc);
+        hq_reader_advance(r->reader, len, 0);
+        const int st = resolve_pending(r);
+        if (st == 1) return 1;
+        if (st == 2) {
+          /* chunk b - 1 was handed back: chunk b (behind it) is dropped unseen -- its kernels were never launched */
+          if ((rc = hpgq_batch_text_cancel(r->ctx[g], s))) return die_hpgq("hpgq_batch_text_cancel", rc);
+          b -= 2; /* the handed-back chunk takes its slot again */
+          continue;
+        }
+        r->pend = 1;
+        r->pend_g = g;
+        r->pend_s = s;
+        r->pend_off = off;
+        r->pend_len = len;
+        continue;
+      }
+      /* no record boundary found inside the budget: the host reader takes over (and owns the messages) */
+      {
+        const int st = resolve_pending(r);
+        if (st == 1) return 1;
+        if (st == 2) {
           b--;
           continue;
         }
       }
-      /* blank lines, a malformed record, no boundary found: the host reader takes over (and owns the messages) */
       r->device_parse = 0;
       logf_("INFO", "device FASTQ parser handed the input back to the host reader");
     }

@@ -85,7 +85,8 @@ typedef struct hpgq_params {
   int32_t k2;              /* second k-mer size (BASELINE: 11), 0 = off, <= 13       */
   int32_t cg_k;            /* chaos-game word size, 1..12                            */
   int32_t cg_base_quality; /* chaos_game_data_t.base_quality (old/chaos_game.h:92)   */
-  int32_t kernel_variant;  /* 0 = auto (tiled fast path), 1 = force simple warp-per-read path */
+  int32_t kernel_variant;  /* 0 = auto (tiled fast path), 1 = force simple warp-per-read path,
+                            * 2 = auto + one-pass edit / filter / compaction kernel (HPGQ_WORK_COMPACT) */
   hpgq_filter_opts_t filter;
   hpgq_edit_opts_t edit;
 } hpgq_params_t;
@@ -229,6 +230,16 @@ typedef struct hpgq_text_info {
   uint32_t reserved;
 } hpgq_text_info_t;
 int hpgq_batch_submit_text(hpgq_ctx_t *ctx, const uint8_t *text, uint64_t n_bytes, int slot, hpgq_text_info_t *info);
+/* The same in two halves, so that a reader can stage the NEXT chunk while the device still parses this one.
+ * hpgq_batch_submit_text_fd reads n_bytes at file_offset of an open file with pread() (a few threads, straight into
+ * the slot's pinned staging: no page faults of a mapped file, no extra copy), queues the host -> device copies and
+ * the parse, and returns without waiting.  hpgq_batch_text_launch then waits for that parse only, fills *info as
+ * hpgq_batch_submit_text does and launches the QC kernels when info->status == 0.  Replaces the fastq_fread_se()
+ * call of the producers (src/stats_fastq.c:183, src/filter_fastq.c:114, src/edit_fastq.c:121). */
+int hpgq_batch_submit_text_fd(hpgq_ctx_t *ctx, int fd, uint64_t file_offset, uint64_t n_bytes, int slot);
+int hpgq_batch_text_launch(hpgq_ctx_t *ctx, int slot, hpgq_text_info_t *info);
+/* drops a chunk submitted with hpgq_batch_submit_text_fd without launching anything for it (the slot is free again) */
+int hpgq_batch_text_cancel(hpgq_ctx_t *ctx, int slot);
 /* Header line of every read of the slot's text batch: byte offset inside `text` and length without the line
  * terminator (n_reads entries each).  Valid between hpgq_batch_submit_text and the next submit on the slot. */
 int hpgq_batch_text_headers(hpgq_ctx_t *ctx, int slot, uint32_t *hdr_off, uint32_t *hdr_len);

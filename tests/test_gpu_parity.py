@@ -176,8 +176,10 @@ def test_device_resident_generator_matches_host(q, ob):
 def test_edit_trim_filter_compact(q, ob, no_fuse, monkeypatch):
     """Both compaction paths: the one-pass kernel (decisions + look-back + output from the staged tile) and the
     two-pass path (decision kernel, scan, gather; HPGQ_NO_FUSE)."""
-    if no_fuse:
-        monkeypatch.setenv("HPGQ_NO_FUSE" if no_fuse == 1 else "HPGQ_FZ_SLOW", "1")
+    if no_fuse != 1:
+        monkeypatch.setenv("HPGQ_FUSE", "1")
+    if no_fuse == 2:
+        monkeypatch.setenv("HPGQ_FZ_SLOW", "1")
     seq, qual, idx = pack(EDIT_READS)
     par = q.make_params(q.WORK_EDIT | q.WORK_FILTER | q.WORK_COMPACT, edit=EDIT_OPTS, filter=dict(min_read_length=3))
     _, res, _, emask, etrim = check(q, ob, par, seq, qual, idx, 8)
@@ -275,8 +277,10 @@ def test_long_reads_group_and_position_kernels(q, ob):
 def test_edit_group_kernel_all_lane_widths(q, ob, lmax, no_fuse, monkeypatch):
     """EDIT + FILTER (+ filter windows) on ragged reads: every lanes-per-read instantiation of the group kernel and
     of the one-pass kernel (reads of 2500 bp take the two-pass path either way)."""
-    if no_fuse:
-        monkeypatch.setenv("HPGQ_NO_FUSE" if no_fuse == 1 else "HPGQ_FZ_SLOW", "1")
+    if no_fuse != 1:
+        monkeypatch.setenv("HPGQ_FUSE", "1")
+    if no_fuse == 2:
+        monkeypatch.setenv("HPGQ_FZ_SLOW", "1")
     rng = np.random.default_rng(lmax)
     seq, qual, idx = rand_batch(rng, 6000, 0, lmax, p_n=0.03)
     qual = rng.integers(35, 74, size=len(qual)).astype(np.uint8)
@@ -523,9 +527,10 @@ def test_chaos_game_exact_inside_a_large_batch(q, ob):
 
 
 @pytest.mark.parametrize("L,n", [(150, 300000), (36, 500000), (1000, 40000)])
-def test_one_pass_compaction_many_tiles(q, ob, L, n):
+def test_one_pass_compaction_many_tiles(q, ob, L, n, monkeypatch):
     """Thousands of tiles through the decoupled look-back: filter-only, edit-only and edit + filter, most reads failing
     (a large failed stream through the side buffer), every read failing, every read passing."""
+    monkeypatch.setenv("HPGQ_FUSE", "1")
     seq, qual, idx = q.synth_host(q.synth_cfg(L, short_pct=4, short_min=max(L // 4, 1)), 5, n)
     edit = dict(left_length=10, min_left_quality=30, right_length=12, min_right_quality=22)
     cases = [(q.WORK_EDIT | q.WORK_FILTER | q.WORK_COMPACT, dict(min_read_length=L // 2, min_read_quality=20, max_N=5)),
@@ -544,10 +549,11 @@ def test_one_pass_compaction_many_tiles(q, ob, L, n):
 
 
 @pytest.mark.parametrize("lmax", [30, 75, 150, 310, 630])
-def test_one_pass_word_frame_decisions_on_ragged_reads(q, ob, lmax):
+def test_one_pass_word_frame_decisions_on_ragged_reads(q, ob, lmax, monkeypatch):
     """The word-frame decision of the one-pass kernel (no filter windows, no out-of-quality limit) in each of its lane
     widths, on reads of every length from 0 up: reads shorter than the two trim windows fall back to the register
     code inside the same warp iteration."""
+    monkeypatch.setenv("HPGQ_FUSE", "1")
     rng = np.random.default_rng(1000 + lmax)
     seq, qual, idx = rand_batch(rng, 20000, 0, lmax, p_n=0.04)
     qual = rng.integers(35, 74, size=len(qual)).astype(np.uint8)

@@ -58,6 +58,9 @@ def main():
     ap.add_argument("--reps", type=int, default=2)
     ap.add_argument("--batch-size", type=int, default=1 << 20)
     ap.add_argument("--dir", default=None)
+    ap.add_argument("--commands", default="stats,filter")
+    ap.add_argument("--parsers", default="device,host")
+    ap.add_argument("--env", action="append", default=[], help="A/B: run every case once more per NAME=VALUE[,NAME=VALUE]")
     args = ap.parse_args()
     import __graft_entry__ as g
     q = g.load_package().hpgq
@@ -69,8 +72,14 @@ def main():
     print(json.dumps({"file": path, "bytes": nbytes, "reads": args.reads, "gen_s": time.perf_counter() - t0}), flush=True)
     cases = [("stats", ["--read-length-range", "50,", "--read-quality-range", "20,", "--max-N", "5"]),
              ("filter", ["--read-length-range", "50,", "--read-quality-range", "20,", "--max-N", "5"])]
-    for command, extra in cases:
-        for parser, pflag in (("device", []), ("host", ["--host-parse"])):
+    envs = [("", dict(os.environ))]
+    for spec in args.env:
+        e = dict(os.environ)
+        e.update(kv.split("=", 1) for kv in spec.split(","))
+        envs.append((spec, e))
+    for command, extra in [c for c in cases if c[0] in args.commands.split(",")]:
+      for parser, pflag in [x for x in (("device", []), ("host", ["--host-parse"])) if x[0] in args.parsers.split(",")]:
+        for env_name, env in envs:
             out = os.path.join(base, f"{command}_{parser}")
             os.makedirs(out, exist_ok=True)
             best = None
@@ -78,7 +87,7 @@ def main():
                 t0 = time.perf_counter()
                 mrl = ["--max-read-length", str(args.len)] if command == "stats" else []
                 r = subprocess.run([cli, command, "-f", path, "-o", out, "--batch-size", str(args.batch_size)] + mrl + extra
-                                   + pflag, capture_output=True, text=True, cwd=out)
+                                   + pflag, capture_output=True, text=True, cwd=out, env=env)
                 dt = time.perf_counter() - t0
                 if r.returncode != 0:
                     print(json.dumps({"command": command, "parser": parser, "error": (r.stdout + r.stderr)[-600:]}), flush=True)
@@ -87,7 +96,7 @@ def main():
                 best = dt if best is None else min(best, dt)
             if best is not None:
                 log = open(os.path.join(out, "hpg-fastq.log")).read().strip().splitlines()
-                print(json.dumps({"command": command, "parser": parser, "wall_s": best, "reads_per_s": args.reads / best,
+                print(json.dumps({"command": command, "parser": parser, "env": env_name, "wall_s": best, "reads_per_s": args.reads / best,
                                   "text_gbs": nbytes / best / 1e9, "batch_size": args.batch_size,
                                   "log": [l for l in log if "reads on" in l or "phases" in l]}), flush=True)
     if not args.dir:
