@@ -433,7 +433,7 @@ __device__ __forceinline__ bool fz_read(const fz_rec *r, uint4 *v) {
   return ((a0 & a1 & a2 & a3) >> 32) != 0ull;
 }
 struct fz_bufs {
-  fz_rec *agg, *incl;       // per tile: its own totals / the totals of all tiles up to and including it
+  fz_rec *agg, *incl;       // agg: a tile's own totals; incl: [0] the batch's totals, then the level-2 and level-3 records
   uint32_t *status;         // status[0] = ticket counter
   uint8_t *fail_seq, *fail_qual;
   uint32_t *fail_idx, *fail_src;
@@ -703,35 +703,46 @@ __global__ void __launch_bounds__(256, 4) hq_fz_kernel(hq_kargs a, hq_compact_bu
       }
       const uint4 agg = make_uint4(__shfl_sync(0xFFFFFFFFu, inc.x, 31), __shfl_sync(0xFFFFFFFFu, inc.y, 31),
                                    __shfl_sync(0xFFFFFFFFu, inc.z, 31), __shfl_sync(0xFFFFFFFFu, inc.w, 31));
-      if (lane == 0) fz_publish(tile == 0 ? &z.incl[0] : &z.agg[tile], agg);
-      uint4 pre = make_uint4(0, 0, 0, 0);
-      if (tile > 0) {
-        // (64 predecessors per round, two per lane, measured slower: 1.89 against 1.19 ms per 2^22 reads -- the wait
-        // is for the NEAREST predecessors' own totals, and a wider window only adds words to poll)
-        int32_t j = (int32_t)tile - 1 - (int32_t)lane;
-        for (;;) {
-          uint4 val = make_uint4(0, 0, 0, 0);
-          uint32_t st;  // 2: totals up to and including tile j, 1: tile j's own totals, 0: nothing yet
-          do {
-            st = 2u;
-            if (j >= 0) st = fz_read(&z.incl[j], &val) ? 2u : (fz_read(&z.agg[j], &val) ? 1u : 0u);
-          } while (__any_sync(0xFFFFFFFFu, st == 0u));
-          const uint32_t done = __ballot_sync(0xFFFFFFFFu, st == 2u);  // j < 0 counts: everything before tile 0 is 0
-          const uint32_t first = done ? (uint32_t)__ffs(done) - 1u : 32u;
-          if (lane > first) val = make_uint4(0, 0, 0, 0);
+      // ---- D: the tile's place in the output from a three-level tree of TOTALS (no chain of inclusive prefixes).
+      // Level 1 = a tile's own totals; the last tile of every group of 32 also sums its group into a level-2 record,
+      // the last tile of every 32 groups those into a level-3 record.  A tile's exclusive prefix is then the sum of
+      // the level-3 records in front of its 1024-group, the level-2 records in front of its group and the level-1
+      // records in front of it inside its group: three sets of independent loads, all requested at once, ONE round
+      // trip to L2 -- and every record it needs was published by a tile that started before it and never waits for
+      // anything.  (The classic look-back walks back window by window to the nearest tile that already knows its
+      // inclusive prefix: with 592 CTAs in flight that cost ~ 17 ns per tile chip-wide, profiles/fused_r2_summary.md.)
+      fz_rec *L1 = z.agg, *L2 = z.incl + 1, *L3 = z.incl + 1 + ((z.n_tiles + 31u) >> 5);
+      if (lane == 0) fz_publish(&L1[tile], agg);
+      auto sum_recs = [&](const fz_rec *base, uint32_t count) -> uint4 {  // sum of base[0 .. count), count <= 32
+        uint4 val = make_uint4(0, 0, 0, 0);
+        bool ok;
+        do {
+          ok = true;
+          if (lane < count) ok = fz_read(&base[lane], &val);
+        } while (!__all_sync(0xFFFFFFFFu, ok));
+        if (lane >= count) val = make_uint4(0, 0, 0, 0);
 #pragma unroll
-          for (int dd = 16; dd > 0; dd >>= 1) {
-            val.x += __shfl_xor_sync(0xFFFFFFFFu, val.x, dd);
-            val.y += __shfl_xor_sync(0xFFFFFFFFu, val.y, dd);
-            val.z += __shfl_xor_sync(0xFFFFFFFFu, val.z, dd);
-            val.w += __shfl_xor_sync(0xFFFFFFFFu, val.w, dd);
-          }
-          pre = add4(pre, val);
-          if (done) break;
-          j -= 32;
+        for (int dd = 16; dd > 0; dd >>= 1) {
+          val.x += __shfl_xor_sync(0xFFFFFFFFu, val.x, dd);
+          val.y += __shfl_xor_sync(0xFFFFFFFFu, val.y, dd);
+          val.z += __shfl_xor_sync(0xFFFFFFFFu, val.z, dd);
+          val.w += __shfl_xor_sync(0xFFFFFFFFu, val.w, dd);
         }
-        if (lane == 0) fz_publish(&z.incl[tile], add4(pre, agg));
+        return val;
+      };
+      const uint32_t t1 = tile & 31u, g2 = tile >> 5, t2 = g2 & 31u, g3 = tile >> 10;
+      const uint4 in_group = sum_recs(&L1[tile - t1], t1);            // tiles of my group in front of me
+      if (t1 == 31u) {                                                // duty: my group's level-2 record
+        const uint4 gsum = add4(in_group, agg);
+        if (lane == 0) fz_publish(&L2[g2], gsum);
+        if (t2 == 31u) {                                              // and the level-3 record of my 32 groups
+          const uint4 ssum = add4(sum_recs(&L2[g2 - 31u], 31u), gsum);
+          if (lane == 0) fz_publish(&L3[g3], ssum);
+        }
       }
+      uint4 pre = add4(in_group, sum_recs(&L2[g2 - t2], t2));
+      for (uint32_t k = 0; k < g3; k += 32u) pre = add4(pre, sum_recs(&L3[k], min(32u, g3 - k)));
+      if (tile == z.n_tiles - 1u && lane == 0) fz_publish(&z.incl[0], add4(pre, agg));  // the batch's totals
       // ---- E: keys of the tile's reads in their streams, source offsets, output offsets / source indices
       uint4 run = make_uint4(pre.x + inc.x - sum.x, pre.y + inc.y - sum.y, pre.z + inc.z - sum.z, pre.w + inc.w - sum.w);
 #pragma unroll
@@ -792,7 +803,7 @@ __global__ void __launch_bounds__(256, 4) hq_fz_kernel(hq_kargs a, hq_compact_bu
 // The failed reads' bytes, offsets and source indices move behind the passed reads; totals for the host.
 __global__ void __launch_bounds__(256) hq_fz_finish(hq_kargs a, hq_compact_bufs b, fz_bufs z) {
   uint4 tot = make_uint4(0, 0, 0, 0);
-  if (z.n_tiles) (void)fz_read(&z.incl[z.n_tiles - 1u], &tot);
+  if (z.n_tiles) (void)fz_read(&z.incl[0], &tot);
   const uint32_t gtid = blockIdx.x * blockDim.x + threadIdx.x, gstride = gridDim.x * blockDim.x;
   const uint32_t D0 = tot.x, D1 = tot.x + tot.y;
   for (uint32_t c = (D0 >> 4) + gtid; c < ((D1 + 15u) >> 4); c += gstride) {
@@ -867,7 +878,10 @@ cudaError_t hq_launch_checksum(const hq_compact_bufs &b, uint32_t n, unsigned lo
 namespace {
 uint32_t fz_rpt(uint32_t max_len) {
   uint32_t rpt = CT_SPAN / (max_len ? max_len : 1u);
-  return rpt > CT_RPT ? CT_RPT : rpt;
+  uint32_t cap = CT_RPT;
+  const char *v = getenv("HPGQ_FZ_RPT");  // developer knob: reads per tile (16..128)
+  if (v && atoi(v) >= 16 && atoi(v) <= (int)CT_RPT) cap = (uint32_t)atoi(v);
+  return rpt > cap ? cap : rpt;
 }
 }  // namespace
 
@@ -894,7 +908,7 @@ cudaError_t hq_launch_fz(const hq_kargs &a, const hq_compact_bufs &b, uint32_t m
   z.n_tiles = (a.n_reads + z.rpt - 1u) / z.rpt;
   cudaError_t e = cudaMemsetAsync(z.status, 0, 4, st);
   if (e == cudaSuccess) e = cudaMemsetAsync(z.agg, 0, (size_t)z.n_tiles * sizeof(fz_rec), st);
-  if (e == cudaSuccess) e = cudaMemsetAsync(z.incl, 0, (size_t)z.n_tiles * sizeof(fz_rec), st);
+  if (e == cudaSuccess) e = cudaMemsetAsync(z.incl, 0, (size_t)(2u + ((z.n_tiles + 31u) >> 5) + ((z.n_tiles + 1023u) >> 10)) * sizeof(fz_rec), st);
   if (e != cudaSuccess) return e;
   const uint32_t smem = (((uint32_t)sizeof(fz_hdr) + 15u) & ~15u) + ct_rmap_bytes(z.cap) + 2u * z.cap;
   const uint32_t span = max_len + 15u;

@@ -39,7 +39,7 @@ __device__ __forceinline__ void acc_word(const hq_kargs &a, uint32_t qw, uint32_
           r.ooq += (qq < a.q_lo) | (qq > a.q_hi);
         }
     } else {
-      r.ooq += hq_ooq_count(qw, m, a.c_lo, a.c_hi);
+      r.ooq += hq_ooq_count(qm, m, a.c_lo, a.c_hi);  // masked word: a neighbouring read's byte >= 128 must not carry in
     }
     r.nN += __popc(__vcmpeq4(sw, 0x4E4E4E4Eu) & m & 0x01010101u);
     r.nGC += __popc((__vcmpeq4(sw, 0x47474747u) | __vcmpeq4(sw, 0x43434343u)) & m & 0x01010101u);

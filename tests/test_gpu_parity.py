@@ -595,3 +595,29 @@ def test_kmers_and_chaos_game_single_reduction_path(q, ob, k2, ck, monkeypatch):
         exp, _, _ = ob.process_batch(par, lay, seq, qual, idx, counters=exp)
         msg = diff_report(q, lay, got, exp)
         assert not msg, msg
+
+
+def test_device_batch_larger_than_the_ctx_limit_is_refused(q):
+    """hpgq_batch_submit_device with COMPACT: a batch whose bases exceed max_bytes_per_batch (the size of the
+    compaction buffers) is refused, not written past the buffers."""
+    seq, qual, idx = q.synth_host(q.synth_cfg(150), 0, 4000)
+    par = q.make_params(q.WORK_FILTER | q.WORK_COMPACT, filter=C2_FILTER)
+    with q.Ctx(0, max_reads=4000, max_bytes=4000 * 150 // 2, max_read_len=160, host_staging=False) as ctx:
+        ctx.set_params(par)
+        b = ctx.upload_batch(seq, qual, idx, max_len=150)
+        with pytest.raises(q.HpgqError, match="max_bytes_per_batch"):
+            ctx.submit_device(b, 0)
+        ctx.free_batch(b)
+
+
+def test_out_of_quality_count_ignores_the_neighbouring_read(q, ob):
+    """A non-ASCII quality byte at the end of the PRECEDING read shares a 32-bit word with this read's first bytes; the
+    long-read group kernel must not let it carry into this read's out-of-quality count."""
+    rng = np.random.default_rng(9)
+    seq, qual, idx = rand_batch(rng, 400, 1100, 1500, p_n=0.01)
+    qual = rng.integers(40, 70, size=len(qual)).astype(np.uint8)
+    for r in range(1, 400, 3):
+        qual[int(idx[r]) - 1] = 250
+    par = q.make_params(q.WORK_STATS | q.WORK_FILTER, filter=dict(min_read_quality=10, max_read_quality=36, max_out_of_quality=128))
+    _, _, _, emask, _ = check(q, ob, par, seq, qual, idx, 1536)
+    assert 0 < int(emask.sum()) < len(emask)
