@@ -800,6 +800,61 @@ __global__ void __launch_bounds__(256, 4) hq_fz_kernel(hq_kargs a, hq_compact_bu
   }
 }
 
+// ---------------------------------------------------------------- decisions only, word frame, straight from global
+// The decision half of the two-pass path (edit / filter without statistics) for the common case fz_decide_fast takes:
+// G lanes per read, K = 5 words per lane read with 4-byte loads at the read's own byte phase (two loads + one PRMT per
+// word; a group's loads cover consecutive 32-byte sectors).  ~ 40 instructions per read against ~ 100 for the
+// register-resident kernel of hpgq_group.cu, which remains for filter windows / out-of-quality limits / longer reads.
+template <int G>
+__global__ void __launch_bounds__(256) hq_dec_fast_kernel(hq_kargs a) {
+  constexpr int K = 5;
+  constexpr uint32_t NG = 32u / G;
+  const uint32_t lane = threadIdx.x & 31u, lig = lane % G, giw = lane / G;
+  const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
+  const bool do_filter = a.work & HPGQ_WORK_FILTER, do_edit = a.work & HPGQ_WORK_EDIT;
+  uint32_t n_pass = 0, n_fail = 0, n_edit = 0;
+  fz_len_consts<K, G> lc;
+  lc.L = 0xFFFFFFFFu;
+  lc.wl = lc.wr = 0u;
+  const uint32_t end_ok = a.idx[a.n_reads] + 32u;
+  const uint32_t *dummy = reinterpret_cast<const uint32_t *>(a.ctr);  // >= 32 u64 scalars + histograms: always readable
+  for (uint32_t r0 = warp * NG; r0 < a.n_reads; r0 += nwarps * NG) {  // warp-uniform trip count (shuffles below)
+    const uint32_t r = r0 + giw;
+    const bool live = r < a.n_reads;
+    const uint32_t o = live ? a.idx[r] : a.idx[0], L = live ? a.idx[r + 1] - o : 0u;
+    if (L != lc.L) fz_len_update<K, G>(a, lc, L, lig);
+    // the frame of the last reads of the batch reaches past the arrays' readable end (idx[n] + 32): those reads take
+    // the register code, whose loads stop at the read's end, and the frame loads of their lanes go to the counter block
+    const bool tail = o + 4u * K * G + 8u > end_ok;
+    const bool slow = lc.wl + lc.wr > L || tail;
+    const uint32_t *ps = tail ? dummy : reinterpret_cast<const uint32_t *>(a.seq) + (o >> 2) + lig;
+    const uint32_t *pq = tail ? dummy : reinterpret_cast<const uint32_t *>(a.qual) + (o >> 2) + lig;
+    fz_dec dec = fz_decide_fast<K, G>(a, lc, ps, pq, 0x3210u + 0x1111u * (o & 3u), do_edit, do_filter);
+    if (__any_sync(0xFFFFFFFFu, slow)) {
+      const fz_dec d2 = fz_decide_regs<G, false>(a, a.seq, a.qual, CT_PAD, o, L, lig, do_edit, do_filter, false);
+      if (slow) dec = d2;
+    }
+    if (live && lig == 0) {
+      n_edit += dec.edited;
+      if (do_filter) {
+        n_pass += dec.pass;
+        n_fail += !dec.pass;
+      }
+      if (a.trim) a.trim[r] = hpgq_trim_t{dec.start, dec.len};
+      if (a.mask) a.mask[r] = dec.pass ? 1 : 0;
+    }
+  }
+  unsigned long long *C = a.ctr;
+  n_pass = group_sum<32>(n_pass);
+  n_fail = group_sum<32>(n_fail);
+  n_edit = group_sum<32>(n_edit);
+  if (lane == 0) {
+    if (n_pass) atomicAdd(&C[HPGQ_S_NUM_PASSED], (unsigned long long)n_pass);
+    if (n_fail) atomicAdd(&C[HPGQ_S_NUM_FAILED], (unsigned long long)n_fail);
+    if (n_edit) atomicAdd(&C[HPGQ_S_NUM_EDITED], (unsigned long long)n_edit);
+  }
+}
+
 // The failed reads' bytes, offsets and source indices move behind the passed reads; totals for the host.
 __global__ void __launch_bounds__(256) hq_fz_finish(hq_kargs a, hq_compact_bufs b, fz_bufs z) {
   uint4 tot = make_uint4(0, 0, 0, 0);
@@ -948,6 +1003,30 @@ cudaError_t hq_launch_fz(const hq_kargs &a, const hq_compact_bufs &b, uint32_t m
     ++*launches;
   }
   hq_fz_finish<<<sm_count * 4, 256, 0, st>>>(a, b, z);
+  ++*launches;
+  return cudaGetLastError();
+}
+
+// returns cudaErrorInvalidValue when the batch / options need the kernels of hpgq_group.cu
+cudaError_t hq_launch_dec_fast(const hq_kargs &a, uint32_t max_len, int sm_count, cudaStream_t st, uint64_t *launches) {
+  if (a.n_reads == 0) return cudaSuccess;
+  if ((a.work & (HPGQ_WORK_STATS | HPGQ_WORK_KMERS | HPGQ_WORK_CHAOS)) || !(a.work & (HPGQ_WORK_EDIT | HPGQ_WORK_FILTER)))
+    return cudaErrorInvalidValue;
+  const bool ooq = (a.work & HPGQ_WORK_FILTER) != 0 && a.max_ooq < 32 * RG_LB;
+  const bool windows = (a.work & HPGQ_WORK_FILTER) != 0 && (a.f_ll > 0 || a.f_rl > 0);
+  if (ooq || windows || a.e_ll > 255 || a.e_rl > 255 || max_len == 0 || max_len > 20u * 32u - 3u || getenv("HPGQ_FZ_SLOW"))
+    return cudaErrorInvalidValue;
+  const int G = max_len <= 77u ? 4 : max_len <= 157u ? 8 : max_len <= 317u ? 16 : 32;
+  const uint32_t rpb = 256u / (uint32_t)G;
+  uint32_t blocks = (a.n_reads + rpb - 1u) / rpb;
+  const uint32_t cap = (uint32_t)sm_count * 8u * 4u;
+  if (blocks > cap) blocks = cap;
+  switch (G) {
+    case 4: hq_dec_fast_kernel<4><<<blocks, 256, 0, st>>>(a); break;
+    case 8: hq_dec_fast_kernel<8><<<blocks, 256, 0, st>>>(a); break;
+    case 16: hq_dec_fast_kernel<16><<<blocks, 256, 0, st>>>(a); break;
+    default: hq_dec_fast_kernel<32><<<blocks, 256, 0, st>>>(a); break;
+  }
   ++*launches;
   return cudaGetLastError();
 }

@@ -75,6 +75,8 @@ struct hq_compact_bufs {
 };
 // decisions (trim, filter) and compaction in one pass over the batch; false = this batch needs the two-pass path
 bool hq_fz_supports(uint32_t work, uint32_t max_len, uint32_t n_reads, const hq_compact_bufs &b);
+// decisions only (edit / filter without statistics), word frame; cudaErrorInvalidValue = use hq_launch_qc_group
+cudaError_t hq_launch_dec_fast(const hq_kargs &a, uint32_t max_len, int sm_count, cudaStream_t st, uint64_t *launches);
 cudaError_t hq_launch_fz(const hq_kargs &a, const hq_compact_bufs &b, uint32_t max_len, int sm_count, cudaStream_t st,
                          uint64_t *launches);
 cudaError_t hq_launch_compact(const hq_kargs &a, const hq_compact_bufs &b, uint32_t mean_len, uint32_t max_len,
