@@ -353,8 +353,14 @@ __device__ __forceinline__ void load8(const uint8_t *base, uint32_t off, uint32_
 // its eight positions of each read from shared memory.  NS - 1 stages (of POS_RB reads x 2 x 2 KB) are in flight per
 // CTA, so HBM latency is hidden without spending registers on loads.  (One 1-D bulk copy per read and array was
 // measured first: ~0.7 M copies of 2 KB per launch sustain only 1.9 TB/s, the TMA engine is op-rate bound there.)
-constexpr int POS_RB = 4;                      // reads per stage
-constexpr int POS_NS = 4;                      // ring depth
+#ifndef HQ_POS_RB
+#define HQ_POS_RB 8   // 8 reads x 3 stages: 1.08 against 1.14 ms per C5 batch with 4 x 4 (profiles/sweep_c5_r2.log)
+#endif
+#ifndef HQ_POS_NS
+#define HQ_POS_NS 3
+#endif
+constexpr int POS_RB = HQ_POS_RB;              // reads per stage (developer knobs: tools/build_variants.sh)
+constexpr int POS_NS = HQ_POS_NS;              // ring depth
 constexpr int POS_SLOT = POS_TILE + 32;        // bytes per read and array in a stage (16-byte aligned superset)
 constexpr int POS_CH = POS_SLOT / 16;          // 16-byte chunks per slot
 
