@@ -374,21 +374,23 @@ def run_config(q, torch, dist, name, c, rank, world, local, peak):
             batches.append((f, ctx.synth_device(scfg, first0 + f, nb, bytes_hint=None if fixed else cap_bytes)))
             f += nb
 
-        def one_pass(collect):
+        def passes(reps):
+            # batches of all passes are queued back to back on the two slots; a slot is awaited only to be reused
             busy = [False, False]
-            for i, (_, b) in enumerate(batches):
-                sl = i & 1
-                if busy[sl]:
-                    ctx.sync(sl)
-                    if collect:
+            k = 0
+            for _ in range(reps):
+                for _, b in batches:
+                    sl = k & 1
+                    k += 1
+                    if busy[sl]:
+                        ctx.sync(sl)
                         kms.append(ctx.last_kernel_ms(sl))
-                ctx.submit_device(b, sl, uniform=c["uniform"] and fixed)
-                busy[sl] = True
+                    ctx.submit_device(b, sl, uniform=c["uniform"] and fixed)
+                    busy[sl] = True
             for sl in (0, 1):
                 if busy[sl]:
                     ctx.sync(sl)
-                    if collect:
-                        kms.append(ctx.last_kernel_ms(sl))
+                    kms.append(ctx.last_kernel_ms(sl))
 
         ctx.counters_reset()
         w = batches[:4]
@@ -402,8 +404,7 @@ def run_config(q, torch, dist, name, c, rank, world, local, peak):
         l0 = ctx.launch_count()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(streams[0])
-        for _ in range(c["reps"]):
-            one_pass(True)
+        passes(c["reps"])
         j = torch.cuda.Event()
         j.record(streams[1])
         streams[0].wait_event(j)
