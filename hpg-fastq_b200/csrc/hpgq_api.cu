@@ -1,7 +1,11 @@
 // hpgq_api.cu -- implementation of the C ABI in include/hpg_fastq_cuda.h.
 // One ctx per GPU, used by one host thread; n_slots streams double-buffer H2D copies against
 // kernels; the flat u64 counter block lives on the device for the whole run.
+#include <atomic>
+#include <condition_variable>
+#include <mutex>
 #include <thread>
+#include <vector>
 #include <cuda_runtime.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -13,6 +17,7 @@
 #include "../../include/hpgq_synth.h"
 
 #define HPGQ_MAX_SLOTS 4
+#define HQ_RING_MAX 8
 
 static thread_local char g_last_error[512] = "";
 
@@ -29,6 +34,15 @@ static int fail_msg(int code, const char *what) {
     cudaError_t e__ = (call);                        \
     if (e__ != cudaSuccess) return fail_cuda(e__, #call); \
   } while (0)
+
+struct hq_ring {
+  uint8_t *base = nullptr;
+  uint64_t piece = 0;
+  int n = 0;
+  uint64_t seq = 0;  // pieces handed out so far
+  cudaEvent_t ev[HQ_RING_MAX] = {};
+  bool used[HQ_RING_MAX] = {};
+};
 
 struct hpgq_slot {
   cudaStream_t stream = nullptr;
@@ -58,16 +72,16 @@ struct hpgq_slot {
   uint8_t *h_out_seq = nullptr, *h_out_qual = nullptr;
   uint32_t *h_out_idx = nullptr, *h_out_src = nullptr, *h_lens = nullptr;
   uint64_t h_out_bytes = 0, h_out_reads = 0;
-  // FASTQ text path (hpgq_batch_submit_text): device chunk, pinned staging, parser scratch
-  uint8_t *d_text = nullptr, *h_text = nullptr;
-  uint64_t d_text_cap = 0, h_text_cap = 0;
+  // FASTQ text path (hpgq_batch_submit_text): device chunk, parser scratch (the pinned staging is the ctx's ring)
+  uint8_t *d_text = nullptr;
+  uint64_t d_text_cap = 0;
   hq_parse_bufs pb = {};
   uint32_t *h_pinfo = nullptr;  // pinned copy of pb.info
   bool text_batch = false;
   bool text_pending = false;         // a chunk is parsed / being parsed, hpgq_batch_text_launch not called yet
   cudaEvent_t ev_parse = nullptr;    // end of the parse chain + info block copy
   uint8_t *d_otext = nullptr, *h_otext = nullptr;  // FASTQ text of the compacted output (hpgq_batch_wait_text)
-  uint64_t otext_cap = 0;
+  uint64_t otext_cap = 0, h_otext_cap = 0;
 };
 
 struct hpgq_ctx {
@@ -86,6 +100,10 @@ struct hpgq_ctx {
   // different slots never queue behind each other inside an ev0..ev1 bracket (each QC kernel fills every SM
   // anyway).  Copies of the next batch still overlap the running kernel.
   cudaEvent_t last_done = nullptr;
+  // FASTQ text path: pinned staging ring shared by the slots.  Pinning costs 0.39 ms per MB on the GPU box
+  // (profiles/probe_alloc_r2.log), so a chunk goes through a few pieces that are reused as soon as their copy is done
+  // instead of through a pinned buffer of its own size.
+  hq_ring ring_in, ring_out;
 };
 
 // ------------------------------------------------------------------ misc
@@ -176,6 +194,13 @@ extern "C" int hpgq_device_count(int *n) {
 }
 
 // ------------------------------------------------------------------ context
+static void ring_free(hq_ring &r) {
+  cudaFreeHost(r.base);
+  for (int i = 0; i < HQ_RING_MAX; ++i)
+    if (r.ev[i]) cudaEventDestroy(r.ev[i]);
+  r = hq_ring();
+}
+
 static void slot_free(hpgq_slot &s) {
   cudaFree(s.d_seq); cudaFree(s.d_qual); cudaFree(s.d_idx);
   cudaFreeHost(s.h_seq); cudaFreeHost(s.h_qual); cudaFreeHost(s.h_idx);
@@ -189,7 +214,7 @@ static void slot_free(hpgq_slot &s) {
   cudaFree(s.cb.fail_seq); cudaFree(s.cb.fail_qual); cudaFree(s.cb.fail_idx); cudaFree(s.cb.fail_src);
   cudaFreeHost(s.h_out_seq); cudaFreeHost(s.h_out_qual); cudaFreeHost(s.h_out_idx); cudaFreeHost(s.h_out_src);
   cudaFreeHost(s.h_lens);
-  cudaFree(s.d_text); cudaFreeHost(s.h_text); cudaFreeHost(s.h_pinfo);
+  cudaFree(s.d_text); cudaFreeHost(s.h_pinfo);
   cudaFree(s.d_otext); cudaFreeHost(s.h_otext);
   cudaFree(s.pb.tile_cnt); cudaFree(s.pb.cta_sum); cudaFree(s.pb.nl); cudaFree(s.pb.info);
   cudaFree(s.pb.seq_off); cudaFree(s.pb.qual_off); cudaFree(s.pb.hdr_off); cudaFree(s.pb.hdr_len);
@@ -205,6 +230,8 @@ extern "C" int hpgq_ctx_destroy(hpgq_ctx_t *ctx) {
   cudaSetDevice(ctx->device);
   cudaDeviceSynchronize();
   for (int i = 0; i < HPGQ_MAX_SLOTS; ++i) slot_free(ctx->slot[i]);
+  ring_free(ctx->ring_in);
+  ring_free(ctx->ring_out);
   cudaFree(ctx->d_ctr);
   cudaFree(ctx->d_cgpack);
   cudaFree(ctx->d_kcpack);

@@ -115,9 +115,12 @@ int hq_reader_scan_prefix(hq_reader_t *r, uint64_t limit, uint32_t *max_line, ui
     const uint8_t *nl = (const uint8_t *)memchr(r->data + hi - 1, '\n', r->size - (hi - 1));
     hi = nl ? (uint64_t)(nl - r->data) + 1 : r->size;
   }
-  enum { T = 4 };
+  enum { T = 16 };
   scan_part_t part[T];
-  const int nt = hi >= (1u << 20) ? T : 1;
+  long ncpu = sysconf(_SC_NPROCESSORS_ONLN);
+  if (getenv("HPGQ_SCAN_THREADS")) ncpu = atol(getenv("HPGQ_SCAN_THREADS")); /* developer knob */
+  const int want = ncpu < 1 ? 1 : (ncpu > T ? T : (int)ncpu);
+  const int nt = hi >= (64u << 20) ? want : (hi >= (1u << 20) ? (want < 4 ? want : 4) : 1);
   const uint64_t per = (hi + (uint64_t)nt - 1) / (uint64_t)nt;
   for (int t = 0; t < nt; t++) {
     part[t].data = r->data;
@@ -276,7 +279,7 @@ int hq_writer_open(const char *path, hq_writer_t **out) {
   *out = NULL;
   hq_writer_t *w = (hq_writer_t *)calloc(1, sizeof *w);
   if (!w) return -1;
-  w->fd = open(path, O_WRONLY | O_CREAT | O_TRUNC, 0644);
+  w->fd = open(path, O_RDWR | O_CREAT | O_TRUNC, 0644); /* read-write: hpgq_batch_wait_text_fd fills it through a mapping */
   w->buf = (uint8_t *)malloc(HQ_WBUF);
   if (w->fd < 0 || !w->buf) {
     if (w->fd >= 0) close(w->fd);
@@ -339,6 +342,11 @@ int hq_writer_put(hq_writer_t *w, const uint8_t *file_data, const hq_host_batch_
     w->buf[w->len++] = '\n';
   }
   return w->failed ? -1 : 0;
+}
+
+int hq_writer_fd(hq_writer_t *w) {
+  wflush(w);
+  return w->failed ? -1 : w->fd;
 }
 
 int hq_writer_put_raw(hq_writer_t *w, const uint8_t *text, uint64_t n) {

@@ -123,6 +123,9 @@ int hq_writer_put(hq_writer_t *w, const uint8_t *file_data, const hq_host_batch_
 
 /* finished FASTQ text (records composed on the device, hpgq_batch_wait_text) */
 int hq_writer_put_raw(hq_writer_t *w, const uint8_t *text, uint64_t n);
+/* flushes the buffered records and returns the descriptor (positioned at the end of what was written), < 0 after a
+ * failed write: for hpgq_batch_wait_text_fd, which appends a device-composed batch itself */
+int hq_writer_fd(hq_writer_t *w);
 
 /* ------------------------------------------------------------------ report */
 typedef struct hq_kmer {

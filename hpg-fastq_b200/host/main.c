@@ -7,18 +7,19 @@
  *                                                                (--host-parse, and input the device parser
  *                                                                hands back: blank lines, malformed records)
  *   worker    fastq_*_worker    (src/stats_fastq.c:202-251, src/filter_fastq.c:134-155, src/edit_fastq.c:142-178)
- *                                                             -> hpgq_batch_submit_text / hpgq_batch_submit
- *                                                                (H2D + kernels, async)
+ *                                                             -> hpgq_batch_submit_text_fd + _text_launch /
+ *                                                                hpgq_batch_submit (H2D + kernels, async)
  *   consumer  fastq_*_consumer  (src/stats_fastq.c:257-417, src/filter_fastq.c:161-176, src/edit_fastq.c:184-208)
- *                                                             -> hpgq_batch_wait + ordered FASTQ writer;
- *                                                                the statistics merge stays on the device
+ *                                                             -> hpgq_batch_wait_text_fd (records composed on
+ *                                                                the GPU, appended to the files) / hpgq_batch_wait
+ *                                                                + FASTQ writer; the statistics merge stays on
+ *                                                                the device
  * with batch b on GPU b mod N, stream slot (b / N) mod 2, so that parsing batch b+1 overlaps the copies and
  * kernels of batch b, and outputs are written in ascending batch order (= input order).
  * There is no CPU fallback: without a B200 the program stops with the library's error.
  */
 #include "hpgq_host.h"
 
-#include <pthread.h>
 #include <stdlib.h>
 #include <string.h>
 #include <time.h>
@@ -57,83 +58,6 @@ static void usage(const char *exec_name) {
   printf("For more information about a certain command, type %s <command> --help\n", exec_name);
 }
 
-/* Writer thread: the text of a device-composed batch (hpgq_batch_wait_text) is written while the main thread
- * stages and submits the next batches.  Jobs are executed in order; a slot's pinned text buffer is reused only
- * after the jobs that point into it are done (wq_wait_for). */
-#define HQ_WQ 16
-typedef struct wjob {
-  hq_writer_t *w;
-  const uint8_t *p;
-  uint64_t n;
-} wjob_t;
-typedef struct wqueue {
-  pthread_t th;
-  pthread_mutex_t mu;
-  pthread_cond_t cv;
-  wjob_t job[HQ_WQ];
-  uint64_t head, tail, done; /* jobs pushed / popped / finished */
-  int started, stop, failed;
-} wqueue_t;
-
-static void *wq_main(void *arg) {
-  wqueue_t *q = (wqueue_t *)arg;
-  pthread_mutex_lock(&q->mu);
-  for (;;) {
-    while (q->tail == q->head && !q->stop) pthread_cond_wait(&q->cv, &q->mu);
-    if (q->tail == q->head) break;
-    const wjob_t j = q->job[q->tail % HQ_WQ];
-    q->tail++;
-    pthread_mutex_unlock(&q->mu);
-    const int bad = hq_writer_put_raw(j.w, j.p, j.n);
-    pthread_mutex_lock(&q->mu);
-    if (bad) q->failed = 1;
-    q->done++;
-    pthread_cond_broadcast(&q->cv);
-  }
-  pthread_mutex_unlock(&q->mu);
-  return NULL;
-}
-
-static int wq_start(wqueue_t *q) {
-  memset(q, 0, sizeof *q);
-  pthread_mutex_init(&q->mu, NULL);
-  pthread_cond_init(&q->cv, NULL);
-  if (pthread_create(&q->th, NULL, wq_main, q)) return -1;
-  q->started = 1;
-  return 0;
-}
-
-/* returns the id to wait for before the memory of this job may be reused */
-static uint64_t wq_push(wqueue_t *q, hq_writer_t *w, const uint8_t *p, uint64_t n) {
-  pthread_mutex_lock(&q->mu);
-  while (q->head - q->done >= HQ_WQ) pthread_cond_wait(&q->cv, &q->mu);
-  q->job[q->head % HQ_WQ] = (wjob_t){w, p, n};
-  const uint64_t id = ++q->head;
-  pthread_cond_broadcast(&q->cv);
-  pthread_mutex_unlock(&q->mu);
-  return id;
-}
-
-static int wq_wait_for(wqueue_t *q, uint64_t id) {
-  if (!q->started) return 0;
-  pthread_mutex_lock(&q->mu);
-  while (q->done < id) pthread_cond_wait(&q->cv, &q->mu);
-  const int bad = q->failed;
-  pthread_mutex_unlock(&q->mu);
-  return bad;
-}
-
-static int wq_finish(wqueue_t *q) {
-  if (!q->started) return 0;
-  pthread_mutex_lock(&q->mu);
-  q->stop = 1;
-  pthread_cond_broadcast(&q->cv);
-  pthread_mutex_unlock(&q->mu);
-  pthread_join(q->th, NULL);
-  q->started = 0;
-  return q->failed;
-}
-
 typedef struct run {
   hq_options_t *o;
   hq_reader_t *reader;
@@ -147,13 +71,14 @@ typedef struct run {
   int device_parse;      /* records are cut on the GPU until a chunk is handed back */
   uint64_t text_budget;  /* bytes of FASTQ text per device-parsed batch */
   uint64_t n_text_batches, n_host_batches;
-  wqueue_t wq;
-  uint64_t wq_id[HQ_MAX_GPUS][HQ_SLOTS]; /* last writer job that reads the slot's text buffer */
   /* the text chunk whose parse is in flight: its QC kernels are launched one chunk later (resolve_pending), so that
    * the next chunk is staged and copied while the device parses this one */
   int pend, pend_g, pend_s;
   uint64_t pend_off, pend_len;
 } run_t;
+
+static double now_s(void);
+static void trace_(const char *what, double since);
 
 /* the pinned SoA arrays are only needed by the host reader: with the device parser they are allocated when (if)
  * the input is handed back (pinning hundreds of MB costs more than parsing them) */
@@ -190,39 +115,25 @@ static int consume(run_t *r, int g, int s) {
   const hq_options_t *o = r->o;
   int rc;
   if (r->is_text[g][s] && o->command != HQ_CMD_STATS) {
-    /* device-parsed batch: the output records were composed on the GPU, the consumer only writes them */
-    const uint8_t *text = NULL;
+    /* device-parsed batch: the output records are composed on the GPU and appended to the files by the library,
+     * piece by piece while the rest is still on its way back (hpgq_batch_wait_text_fd) */
     uint64_t pbytes = 0, fbytes = 0;
-    if (wq_wait_for(&r->wq, r->wq_id[g][s])) { /* the slot's text buffer is about to be overwritten */
+    const int fdp = r->w_pass ? hq_writer_fd(r->w_pass) : -1, fdf = r->w_fail ? hq_writer_fd(r->w_fail) : -1;
+    if ((r->w_pass && fdp < 0) || (r->w_fail && fdf < 0)) {
       fprintf(stderr, "\nFATAL: write error on the output FASTQ files\n");
       return 1;
     }
-    if ((rc = hpgq_batch_wait_text(r->ctx[g], s, &res, &text, &pbytes, &fbytes))) return die_hpgq("hpgq_batch_wait_text", rc);
+    if ((rc = hpgq_batch_wait_text_fd(r->ctx[g], s, &res, fdp, fdf, &pbytes, &fbytes))) return die_hpgq("hpgq_batch_wait_text_fd", rc);
     r->busy[g][s] = 0;
     r->num_reads += res.n_reads;
     r->num_edited += res.n_edited;
-    const int filtering_t = o->command == HQ_CMD_FILTER || o->filter_on;
-    if (filtering_t) {
+    if (o->command == HQ_CMD_FILTER || o->filter_on) {
       r->num_passed += res.n_passed;
       r->num_failed += res.n_failed;
     }
-    if (fbytes && !r->w_fail) {
-      fprintf(stderr, "\nFATAL: failed reads without a failed.fq\n");
-      return 1;
-    }
-    if (!r->wq.started && wq_start(&r->wq)) {
-      fprintf(stderr, "\nFATAL: cannot start the writer thread\n");
-      return 1;
-    }
-    if (pbytes) r->wq_id[g][s] = wq_push(&r->wq, r->w_pass, text, pbytes);
-    if (fbytes) r->wq_id[g][s] = wq_push(&r->wq, r->w_fail, text + pbytes, fbytes);
     return 0;
   }
-  /* host-parsed batch: written here, after whatever the writer thread still holds (same files, same order) */
-  if (wq_wait_for(&r->wq, r->wq.head)) {
-    fprintf(stderr, "\nFATAL: write error on the output FASTQ files\n");
-    return 1;
-  }
+  /* host-parsed batch: the records are formatted here */
   rc = hpgq_batch_wait(r->ctx[g], s, &res);
   if (rc) return die_hpgq("hpgq_batch_wait", rc);
   r->busy[g][s] = 0;
@@ -294,7 +205,9 @@ static int run_pipeline(run_t *r) {
         continue;
       }
     }
+    double tt = now_s();
     if (r->busy[g][s] && consume(r, g, s)) return 1;
+    trace_("  consume", tt);
     hq_host_batch_t *hb = &r->hb[g][s];
     if (r->device_parse) {
       uint64_t off = 0, len = 0;
@@ -312,27 +225,14 @@ static int run_pipeline(run_t *r) {
         /* chunk b is read (pread threads, pinned staging), copied and parsed while chunk b - 1 is still being parsed;
          * only then are the kernels of chunk b - 1 launched */
         int rc;
-        if (getenv("HPGQ_TEXT_SYNC")) { /* developer A/B: the one-call form (copy from the mapping, parse awaited at once) */
-          hpgq_text_info_t info;
-          rc = hpgq_batch_submit_text(r->ctx[g], hq_reader_data(r->reader) + off, len, s, &info);
-          if (rc) return die_hpgq("hpgq_batch_submit_text", rc);
-          if (info.status == 0) {
-            hb->n_reads = info.n_reads;
-            hb->max_len = info.max_len;
-            hq_reader_advance(r->reader, len, info.n_reads);
-            r->busy[g][s] = 1;
-            r->is_text[g][s] = 1;
-            r->n_text_batches++;
-            continue;
-          }
-          r->device_parse = 0;
-          b--;
-          continue;
-        }
+        tt = now_s();
         rc = hpgq_batch_submit_text_fd(r->ctx[g], hq_reader_fd(r->reader), off, len, s);
         if (rc) return die_hpgq("hpgq_batch_submit_text_fd", rc);
+        trace_("  submit_text_fd", tt);
         hq_reader_advance(r->reader, len, 0);
+        tt = now_s();
         const int st = resolve_pending(r);
+        trace_("  text_launch (previous)", tt);
         if (st == 1) return 1;
         if (st == 2) {
           /* chunk b - 1 was handed back: chunk b (behind it) is dropped unseen -- its kernels were never launched */
@@ -384,6 +284,17 @@ static int run_pipeline(run_t *r) {
   return 0;
 }
 
+static double now_s(void);
+static void trace_(const char *what, double since) {
+  static int on = -1;
+  if (on < 0) on = getenv("HPGQ_TRACE") != NULL; /* developer knob: where the wall time of a run goes */
+  if (on) {
+    struct timespec ts;
+    clock_gettime(CLOCK_REALTIME, &ts);
+    fprintf(stderr, "[trace] %-28s %8.3f ms   (epoch %.3f)\n", what, (now_s() - since) * 1e3, (double)ts.tv_sec + 1e-9 * (double)ts.tv_nsec);
+  }
+}
+
 static double now_s(void) {
   struct timespec ts;
   clock_gettime(CLOCK_MONOTONIC, &ts);
@@ -405,6 +316,7 @@ static int run_command(hq_options_t *o) {
     fprintf(stderr, "\nFATAL: cannot open %s\n", o->in_filename);
     goto out;
   }
+  trace_("reader open", t0);
   /* Lcap (entries of the per-position tables) and the batch byte capacity come from the longest line */
   uint32_t max_line = (uint32_t)o->max_read_len;
   if (max_line == 0) {
@@ -417,6 +329,7 @@ static int run_command(hq_options_t *o) {
       goto out;
     }
   }
+  trace_("longest-line scan (cum.)", t0);
   if (max_line == 0) max_line = 1;
   uint64_t cap_bytes = (uint64_t)o->batch_size * max_line;
   if (cap_bytes > (1ull << 30)) cap_bytes = 1ull << 30; /* batches are cut by bytes first for long reads */
@@ -429,6 +342,7 @@ static int run_command(hq_options_t *o) {
     die_hpgq("hpgq_device_count", rc ? rc : HPGQ_ERR_NO_DEVICE);
     goto out;
   }
+  trace_("device count (cum.)", t0);
   r->n_gpus = o->gpus;
   if (r->n_gpus > ndev) {
     fprintf(stderr, "\nFATAL: --gpus %d but only %d CUDA device(s) are visible\n", o->gpus, ndev);
@@ -461,7 +375,15 @@ static int run_command(hq_options_t *o) {
         goto out;
       }
   }
+  trace_("ctx + host batches (cum.)", t0);
   r->device_parse = !o->host_parse;
+  if (r->device_parse)
+    for (int g = 0; g < r->n_gpus; g++)
+      if ((rc = hpgq_ctx_reserve_text(r->ctx[g], 2 * cap_bytes, o->command != HQ_CMD_STATS))) {
+        die_hpgq("hpgq_ctx_reserve_text", rc);
+        goto out;
+      }
+  trace_("text buffers (cum.)", t0);
   r->text_budget = 2 * cap_bytes; /* bases are less than half of the text, so a chunk never exceeds cap_bytes bases */
   if (o->paired && o->command != HQ_CMD_STATS) {
     /* paired end: one .valid (and .invalid) file per mate file (old/README:78,115-118) */
@@ -487,10 +409,6 @@ static int run_command(hq_options_t *o) {
 
   const double t1 = now_s();
   if (run_pipeline(r)) goto out;
-  if (wq_finish(&r->wq)) {
-    fprintf(stderr, "\nFATAL: write error on the output FASTQ files\n");
-    goto out;
-  }
   const double t2 = now_s();
 
   if (r->w_pass && hq_writer_close(r->w_pass)) {
@@ -576,15 +494,18 @@ static int run_command(hq_options_t *o) {
   }
   status = 0;
 out:
-  wq_finish(&r->wq);
+  trace_("run (cum.)", t0);
   if (r->w_pass) hq_writer_close(r->w_pass);
   if (r->w_fail) hq_writer_close(r->w_fail);
+  trace_("writers closed (cum.)", t0);
   for (int g = 0; g < HQ_MAX_GPUS; g++) {
     if (r->ctx[g]) hpgq_ctx_destroy(r->ctx[g]);
     for (int s = 0; s < HQ_SLOTS; s++) free_host_batch(&r->hb[g][s]);
   }
+  trace_("contexts destroyed (cum.)", t0);
   if (r->reader) hq_reader_close(r->reader);
   free(r);
+  trace_("reader closed (cum.)", t0);
   return status;
 }
 

@@ -105,7 +105,7 @@ EXPORTS = [
     "hpgq_strerror", "hpgq_last_error", "hpgq_layout", "hpgq_device_count", "hpgq_ctx_create", "hpgq_ctx_destroy",
     "hpgq_set_params", "hpgq_get_layout", "hpgq_batch_submit", "hpgq_batch_submit_device", "hpgq_batch_wait",
     "hpgq_batch_submit_text", "hpgq_batch_submit_text_fd", "hpgq_batch_text_launch", "hpgq_batch_text_cancel", "hpgq_batch_text_headers",
-    "hpgq_batch_wait_text",
+    "hpgq_batch_wait_text", "hpgq_batch_wait_text_fd", "hpgq_ctx_reserve_text",
     "hpgq_batch_sync", "hpgq_batch_device_views", "hpgq_batch_checksum", "hpgq_checksum_host", "hpgq_counters_reset", "hpgq_counters_download",
     "hpgq_counters_device_ptr", "hpgq_counters_reduce", "hpgq_counters_finalize_host", "hpgq_slot_stream", "hpgq_launch_count",
     "hpgq_last_kernel_ms", "hpgq_synth_device", "hpgq_synth_host", "hpgq_dev_alloc", "hpgq_dev_free",
@@ -272,6 +272,27 @@ class Ctx:
         raw = C.string_at(text.value, tot) if tot else b""
         return dict(n_reads=r.n_reads, n_passed=r.n_passed, n_failed=r.n_failed, n_edited=r.n_edited,
                     passed_text=raw[:pb.value], failed_text=raw[pb.value:])
+
+    def wait_text_fd(self, fd_passed: int, fd_failed: int, slot: int = 0) -> dict:
+        """hpgq_batch_wait_text_fd: the output records are appended to the two descriptors (-1: none expected)."""
+        r = Result()
+        pb, fb = C.c_uint64(0), C.c_uint64(0)
+        _ck(self.lib.hpgq_batch_wait_text_fd(self.h, C.c_int(slot), C.byref(r), C.c_int(fd_passed), C.c_int(fd_failed),
+                                             C.byref(pb), C.byref(fb)), "hpgq_batch_wait_text_fd")
+        return dict(n_reads=r.n_reads, n_passed=r.n_passed, n_failed=r.n_failed, n_edited=r.n_edited,
+                    passed_bytes=pb.value, failed_bytes=fb.value)
+
+    def submit_text_fd(self, fd: int, offset: int, n_bytes: int, slot: int = 0):
+        _ck(self.lib.hpgq_batch_submit_text_fd(self.h, C.c_int(fd), C.c_uint64(offset), C.c_uint64(n_bytes), C.c_int(slot)),
+            "hpgq_batch_submit_text_fd")
+
+    def text_launch(self, slot: int = 0) -> TextInfo:
+        info = TextInfo()
+        _ck(self.lib.hpgq_batch_text_launch(self.h, C.c_int(slot), C.byref(info)), "hpgq_batch_text_launch")
+        return info
+
+    def reserve_text(self, chunk_bytes: int, with_output: bool = False):
+        _ck(self.lib.hpgq_ctx_reserve_text(self.h, C.c_uint64(chunk_bytes), C.c_int(int(with_output))), "hpgq_ctx_reserve_text")
 
     def wait(self, slot: int = 0) -> dict:
         r = Result()

@@ -231,9 +231,9 @@ typedef struct hpgq_text_info {
 } hpgq_text_info_t;
 int hpgq_batch_submit_text(hpgq_ctx_t *ctx, const uint8_t *text, uint64_t n_bytes, int slot, hpgq_text_info_t *info);
 /* The same in two halves, so that a reader can stage the NEXT chunk while the device still parses this one.
- * hpgq_batch_submit_text_fd reads n_bytes at file_offset of an open file with pread() (a few threads, straight into
- * the slot's pinned staging: no page faults of a mapped file, no extra copy), queues the host -> device copies and
- * the parse, and returns without waiting.  hpgq_batch_text_launch then waits for that parse only, fills *info as
+ * hpgq_batch_submit_text_fd reads n_bytes at file_offset of an open file with pread() (a pool of host threads,
+ * straight into a small ring of pinned pieces the ctx owns: no page faults of a mapped file, no extra copy, no
+ * chunk-sized pinned buffer), queues the host -> device copy of every piece and the parse, and returns without waiting.  hpgq_batch_text_launch then waits for that parse only, fills *info as
  * hpgq_batch_submit_text does and launches the QC kernels when info->status == 0.  Replaces the fastq_fread_se()
  * call of the producers (src/stats_fastq.c:183, src/filter_fastq.c:114, src/edit_fastq.c:121). */
 int hpgq_batch_submit_text_fd(hpgq_ctx_t *ctx, int fd, uint64_t file_offset, uint64_t n_bytes, int slot);
@@ -251,6 +251,16 @@ int hpgq_batch_text_headers(hpgq_ctx_t *ctx, int slot, uint32_t *hdr_off, uint32
  * records.  res gets the counts (n_reads, n_passed, n_failed, n_edited) and no array views. */
 int hpgq_batch_wait_text(hpgq_ctx_t *ctx, int slot, hpgq_batch_result_t *res, const uint8_t **text,
                          uint64_t *passed_bytes, uint64_t *failed_bytes);
+/* The same with the writing included (the whole fastq_fwrite() stage): the passed reads' records are appended to
+ * fd_passed and the failed reads' records to fd_failed, each at the descriptor's file position, while the rest of
+ * the text is still on its way back through the ctx's pinned output ring -- no chunk-sized host buffer.  A regular
+ * file opened read-write is extended and filled through a mapping by the pool threads; any other descriptor gets
+ * write().  A descriptor may be -1 when the batch has no records for it (edit without filter: no failed reads). */
+int hpgq_batch_wait_text_fd(hpgq_ctx_t *ctx, int slot, hpgq_batch_result_t *res, int fd_passed, int fd_failed,
+                            uint64_t *passed_bytes, uint64_t *failed_bytes);
+/* Optional: allocates the text path's buffers (pinned rings, per-slot device chunk + parser scratch, and with
+ * with_output != 0 the output text buffers) for chunks of up to chunk_bytes now instead of on the first chunk. */
+int hpgq_ctx_reserve_text(hpgq_ctx_t *ctx, uint64_t chunk_bytes, int with_output);
 /* Blocks until the slot's work is finished and fills the result views. */
 int hpgq_batch_wait(hpgq_ctx_t *ctx, int slot, hpgq_batch_result_t *res);
 /* Same but copies nothing back (device-resident measurement); counters keep accumulating. */

@@ -200,3 +200,48 @@ def test_output_records_composed_on_the_device(q, ob, eol, work_filter):
     assert res["passed_text"] == records(0, npass)
     assert res["failed_text"] == records(npass, n)
     assert res["n_edited"] == int((etrim[:, 1] != np.diff(idx.astype(np.int64))).sum())
+
+
+@pytest.mark.parametrize("piece_mb,out_write", [(1, False), (1, True), (32, False)])
+def test_text_from_a_file_to_files_through_the_pinned_rings(q, ob, tmp_path, monkeypatch, piece_mb, out_write):
+    """hpgq_batch_submit_text_fd + hpgq_batch_text_launch + hpgq_batch_wait_text_fd: the chunk is read from the file in
+    pieces of the pinned ring (1 MB pieces here: many pieces, the ring wraps several times), and the output records go
+    to two descriptors, appended after what they already hold -- the same bytes as hpgq_batch_wait_text returns."""
+    monkeypatch.setenv("HPGQ_PIECE_MB", str(piece_mb))
+    monkeypatch.setenv("HPGQ_RING", "3")
+    if out_write:
+        monkeypatch.setenv("HPGQ_OUT_WRITE", "1")
+    import os
+    n = 40000
+    cfg = q.synth_cfg((20, 150), short_pct=2)
+    seq, qual, idx = q.synth_host(cfg, 11, n)
+    text, _, _ = make_text(seq, qual, idx)
+    src = tmp_path / "in.fq"
+    lead = b"@skipped\nAC\n+\nII\n"
+    src.write_bytes(lead + text)
+    par = q.make_params(q.WORK_EDIT | q.WORK_COMPACT | q.WORK_FILTER, filter=FILTER,
+                        edit=dict(left_length=10, min_left_quality=20, right_length=10, min_right_quality=20))
+    with q.Ctx(0, max_reads=n, max_bytes=int(idx[-1]) + 64, max_read_len=192) as ctx:
+        ctx.set_params(par)
+        ctx.reserve_text(len(text), with_output=True)
+        info = ctx.submit_text(text, 1)
+        assert info.status == 0
+        ref = ctx.wait_text(1)
+        fd = os.open(src, os.O_RDONLY)
+        fp = os.open(tmp_path / "passed.fq", os.O_RDWR | os.O_CREAT | os.O_TRUNC, 0o644)
+        ff = os.open(tmp_path / "failed.fq", os.O_RDWR | os.O_CREAT | os.O_TRUNC, 0o644)
+        os.write(fp, b"already here\n")
+        try:
+            for rep in range(2):  # twice: the second batch is appended behind the first
+                ctx.submit_text_fd(fd, len(lead), len(text), 0)
+                info = ctx.text_launch(0)
+                assert info.status == 0 and info.n_reads == n
+                res = ctx.wait_text_fd(fp, ff, 0)
+                assert res["n_passed"] == ref["n_passed"] and res["n_edited"] == ref["n_edited"]
+                assert res["passed_bytes"] == len(ref["passed_text"]) and res["failed_bytes"] == len(ref["failed_text"])
+        finally:
+            for d in (fd, fp, ff):
+                os.close(d)
+    assert len(ref["passed_text"]) > (2 << 20) and len(ref["failed_text"]) > 0
+    assert (tmp_path / "passed.fq").read_bytes() == b"already here\n" + ref["passed_text"] * 2
+    assert (tmp_path / "failed.fq").read_bytes() == ref["failed_text"] * 2

@@ -60,6 +60,7 @@ def main():
     ap.add_argument("--dir", default=None)
     ap.add_argument("--commands", default="stats,filter")
     ap.add_argument("--parsers", default="device,host")
+    ap.add_argument("--scan", action="store_true", help="stats without --max-read-length: the program scans the file for the longest line")
     ap.add_argument("--env", action="append", default=[], help="A/B: run every case once more per NAME=VALUE[,NAME=VALUE]")
     args = ap.parse_args()
     import __graft_entry__ as g
@@ -85,7 +86,8 @@ def main():
             best = None
             for _ in range(args.reps):
                 t0 = time.perf_counter()
-                mrl = ["--max-read-length", str(args.len)] if command == "stats" else []
+                e0 = time.time()
+                mrl = ["--max-read-length", str(args.len)] if command == "stats" and not args.scan else []
                 r = subprocess.run([cli, command, "-f", path, "-o", out, "--batch-size", str(args.batch_size)] + mrl + extra
                                    + pflag, capture_output=True, text=True, cwd=out, env=env)
                 dt = time.perf_counter() - t0
@@ -94,11 +96,16 @@ def main():
                     best = None
                     break
                 best = dt if best is None else min(best, dt)
+                trace = [l for l in r.stderr.splitlines() if l.startswith("[trace]")]  # HPGQ_TRACE=1
+                if trace:
+                    trace = [f"[trace] spawned at epoch {e0:.3f}, returned at {time.time():.3f}"] + trace
             if best is not None:
                 log = open(os.path.join(out, "hpg-fastq.log")).read().strip().splitlines()
                 print(json.dumps({"command": command, "parser": parser, "env": env_name, "wall_s": best, "reads_per_s": args.reads / best,
                                   "text_gbs": nbytes / best / 1e9, "batch_size": args.batch_size,
                                   "log": [l for l in log if "reads on" in l or "phases" in l]}), flush=True)
+                for l in trace:
+                    print(l, flush=True)
     if not args.dir:
         subprocess.run(["rm", "-rf", base])
 
