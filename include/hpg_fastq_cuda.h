@@ -287,6 +287,10 @@ int hpgq_counters_device_ptr(hpgq_ctx_t *ctx, uint64_t **dptr, size_t *n_words);
  * reference (its consumer is a single thread, src/stats_fastq.c:257-417); NCCL is bound with dlopen at the
  * first call.  n == 1 is a no-op. */
 int hpgq_counters_reduce(hpgq_ctx_t **ctxs, int n);
+/* Optional: creates the communicators hpgq_counters_reduce needs for contexts on these devices (in this order) now;
+ * they are cached per device list for the life of the process.  May run in a host thread of its own while contexts
+ * are created and batches submitted: creating communicators takes 0.5-1 s, the allreduce itself microseconds. */
+int hpgq_comm_prepare(const int *devices, int n);
 /* Fill the derived scalars (totals, min/max length) of a host copy, e.g. after an allreduce. */
 int hpgq_counters_finalize_host(const hpgq_layout_t *layout, uint64_t *block);
 

@@ -60,6 +60,7 @@ def main():
     ap.add_argument("--dir", default=None)
     ap.add_argument("--commands", default="stats,filter")
     ap.add_argument("--parsers", default="device,host")
+    ap.add_argument("--gpus", default="1", help="comma list: the program's --gpus N, one run per value")
     ap.add_argument("--scan", action="store_true", help="stats without --max-read-length: the program scans the file for the longest line")
     ap.add_argument("--env", action="append", default=[], help="A/B: run every case once more per NAME=VALUE[,NAME=VALUE]")
     args = ap.parse_args()
@@ -78,34 +79,37 @@ def main():
         e = dict(os.environ)
         e.update(kv.split("=", 1) for kv in spec.split(","))
         envs.append((spec, e))
-    for command, extra in [c for c in cases if c[0] in args.commands.split(",")]:
-      for parser, pflag in [x for x in (("device", []), ("host", ["--host-parse"])) if x[0] in args.parsers.split(",")]:
-        for env_name, env in envs:
-            out = os.path.join(base, f"{command}_{parser}")
-            os.makedirs(out, exist_ok=True)
-            best = None
-            for _ in range(args.reps):
-                t0 = time.perf_counter()
-                e0 = time.time()
-                mrl = ["--max-read-length", str(args.len)] if command == "stats" and not args.scan else []
-                r = subprocess.run([cli, command, "-f", path, "-o", out, "--batch-size", str(args.batch_size)] + mrl + extra
-                                   + pflag, capture_output=True, text=True, cwd=out, env=env)
-                dt = time.perf_counter() - t0
-                if r.returncode != 0:
-                    print(json.dumps({"command": command, "parser": parser, "error": (r.stdout + r.stderr)[-600:]}), flush=True)
-                    best = None
-                    break
-                best = dt if best is None else min(best, dt)
-                trace = [l for l in r.stderr.splitlines() if l.startswith("[trace]")]  # HPGQ_TRACE=1
-                if trace:
-                    trace = [f"[trace] spawned at epoch {e0:.3f}, returned at {time.time():.3f}"] + trace
-            if best is not None:
-                log = open(os.path.join(out, "hpg-fastq.log")).read().strip().splitlines()
-                print(json.dumps({"command": command, "parser": parser, "env": env_name, "wall_s": best, "reads_per_s": args.reads / best,
-                                  "text_gbs": nbytes / best / 1e9, "batch_size": args.batch_size,
-                                  "log": [l for l in log if "reads on" in l or "phases" in l]}), flush=True)
-                for l in trace:
-                    print(l, flush=True)
+    parsers = [x for x in (("device", []), ("host", ["--host-parse"])) if x[0] in args.parsers.split(",")]
+    combos = [(c, e, p, f, g, en, ev) for c, e in cases if c in args.commands.split(",") for p, f in parsers
+              for g in [int(x) for x in args.gpus.split(",")] for en, ev in envs]
+    for command, extra, parser, pflag, ngpu, env_name, env in combos:
+        out = os.path.join(base, f"{command}_{parser}")
+        os.makedirs(out, exist_ok=True)
+        best, trace = None, []
+        mrl = ["--max-read-length", str(args.len)] if command == "stats" and not args.scan else []
+        argv = [cli, command, "-f", path, "-o", out, "--batch-size", str(args.batch_size)] + mrl + extra + pflag
+        if ngpu != 1:
+            argv += ["--gpus", str(ngpu)]
+        for _ in range(args.reps):
+            t0 = time.perf_counter()
+            e0 = time.time()
+            r = subprocess.run(argv, capture_output=True, text=True, cwd=out, env=env)
+            dt = time.perf_counter() - t0
+            if r.returncode != 0:
+                print(json.dumps({"command": command, "parser": parser, "gpus": ngpu, "error": (r.stdout + r.stderr)[-600:]}), flush=True)
+                best = None
+                break
+            best = dt if best is None else min(best, dt)
+            trace = [l for l in r.stderr.splitlines() if l.startswith("[trace]")]  # HPGQ_TRACE=1
+            if trace:
+                trace = [f"[trace] spawned at epoch {e0:.3f}, returned at {time.time():.3f}"] + trace
+        if best is not None:
+            log = open(os.path.join(out, "hpg-fastq.log")).read().strip().splitlines()
+            print(json.dumps({"command": command, "parser": parser, "gpus": ngpu, "env": env_name, "wall_s": best,
+                              "reads_per_s": args.reads / best, "text_gbs": nbytes / best / 1e9, "batch_size": args.batch_size,
+                              "log": [l for l in log if "reads on" in l or "phases" in l]}), flush=True)
+            for l in trace:
+                print(l, flush=True)
     if not args.dir:
         subprocess.run(["rm", "-rf", base])
 
