@@ -446,15 +446,23 @@ __global__ void __launch_bounds__(POS_THREADS, 2) hq_pos_kernel(hq_kargs a, uint
     }
     if (exhausted && lane == 0) sm.total = appended;
   };
-  // all threads: copies of the stage of iteration j, arriving on its barrier
+  // all threads: copies of the stage of iteration j, arriving on its barrier.  Warp w copies read w (w + 8, ...) of the
+  // stage: one descriptor per warp (a broadcast load), a lane's chunks are lane, lane + 32, ... of both arrays, so a
+  // copy instruction of a warp moves 512 contiguous bytes and the per-chunk index arithmetic is one add
   auto issue = [&](uint32_t j) {
     const uint32_t s = j % POS_NS, tot = sm.total;
-    for (uint32_t i = tid; i < (uint32_t)(2 * POS_RB * POS_CH); i += POS_THREADS) {
-      const uint32_t pair = i / POS_CH, ch = i - pair * POS_CH, k = pair >> 1, arr = pair & 1u;
+    for (uint32_t k = warp; k < (uint32_t)POS_RB; k += POS_THREADS / 32) {
       const uint32_t ei = POS_RB * j + k;
       if (ei < tot) {
         const pos_entry e = sm.fifo[ei % POS_FIFO];
-        if (16u * ch < e.gb) hq_cp_async16(sm.buf[s][k][arr] + 16u * ch, (arr ? a.qual : a.seq) + e.ga + 16u * ch);
+        const uint8_t *gs = a.seq + e.ga, *gq = a.qual + e.ga;
+        uint8_t *ds = sm.buf[s][k][0], *dq = sm.buf[s][k][1];
+#pragma unroll
+        for (uint32_t off = 16u * lane; off < 16u * (uint32_t)POS_CH; off += 512u)
+          if (off < e.gb) {
+            hq_cp_async16(ds + off, gs + off);
+            hq_cp_async16(dq + off, gq + off);
+          }
       }
     }
     hq_cp_async_arrive_noinc(&sm.full[s]);
@@ -501,14 +509,36 @@ __global__ void __launch_bounds__(POS_THREADS, 2) hq_pos_kernel(hq_kargs a, uint
       const pos_entry e = sm.fifo[ei % POS_FIFO];
       const uint32_t L = ei < tot ? e.L : 0u;
       if (p < L && !(a.work & 0x8000u)) {
-        const uint32_t x = e.delta + tid * POS_PER;
+        // 16 bytes around the thread's eight: the byte phase (delta & 7) is the same for every thread of the CTA, so
+        // the funnel is a uniform choice of three words and one PRMT per output word
+        const uint32_t x = e.delta + tid * POS_PER, sh = e.delta & 7u;
+        const uint2 *ws = reinterpret_cast<const uint2 *>(sm.buf[s][k][0] + (x & ~7u));
+        const uint2 *wq = reinterpret_cast<const uint2 *>(sm.buf[s][k][1] + (x & ~7u));
+        const uint2 s0 = ws[0], s1 = ws[1], q0 = wq[0], q1 = wq[1];
+        const uint32_t fsel = 0x3210u + 0x1111u * (sh & 3u);
         uint32_t sv[2], qv[2];
-        lds8(sm.buf[s][k][0], x, sv[0], sv[1]);
-        lds8(sm.buf[s][k][1], x, qv[0], qv[1]);
+        if (sh & 4u) {
+          sv[0] = hq_prmt_raw(s0.y, s1.x, fsel);
+          sv[1] = hq_prmt_raw(s1.x, s1.y, fsel);
+          qv[0] = hq_prmt_raw(q0.y, q1.x, fsel);
+          qv[1] = hq_prmt_raw(q1.x, q1.y, fsel);
+        } else {
+          sv[0] = hq_prmt_raw(s0.x, s0.y, fsel);
+          sv[1] = hq_prmt_raw(s0.y, s1.x, fsel);
+          qv[0] = hq_prmt_raw(q0.x, q0.y, fsel);
+          qv[1] = hq_prmt_raw(q0.y, q1.x, fsel);
+        }
+        if (p + POS_PER > L) {  // the thread that holds the read's end: bytes past it become 0x00, no symbol
+#pragma unroll
+          for (int w = 0; w < 2; ++w) {
+            const uint32_t m = hq_tail_mask(p + 4u * w, L);
+            sv[w] &= m;
+            qv[w] &= m;
+          }
+        }
 #pragma unroll
         for (int w = 0; w < 2; ++w) {
-          const uint32_t m = hq_tail_mask(p + 4u * w, L);
-          const uint32_t sw = sv[w] & m, qm = qv[w] & m;  // bytes past the read end become 0x00: no symbol
+          const uint32_t sw = sv[w], qm = qv[w];
           // four bases per PRMT: the low three bits of a byte select from 8-entry LUTs of 4-bit one-hots (C | G << 4,
           // A | T << 4, N) and of the expected byte; a word with a byte the LUT does not reproduce (lower case,
           // IUPAC, ...) is re-done byte by byte
