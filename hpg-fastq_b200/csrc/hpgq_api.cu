@@ -29,6 +29,8 @@ static int fail_msg(int code, const char *what) {
   snprintf(g_last_error, sizeof g_last_error, "%s", what);
   return code;
 }
+int hq_fail_msg(int code, const char *what) { return fail_msg(code, what); }
+int hq_fail_cuda(cudaError_t e, const char *what) { return fail_cuda(e, what); }
 #define CK(call)                                     \
   do {                                               \
     cudaError_t e__ = (call);                        \

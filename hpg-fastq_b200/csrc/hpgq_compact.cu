@@ -5,7 +5,9 @@
 //
 // Three steps: per-read (bytes, count) records -> exclusive scan (block scan + block-sum scan +
 // add) -> warp-per-read copy of seq and qual bytes to their final offsets.
+#include <pthread.h>
 #include <stdlib.h>
+#include <string.h>
 #include "hpgq_dev.cuh"
 #include "hpgq_internal.h"
 #include "hpgq_regs.cuh"
@@ -1063,4 +1065,85 @@ cudaError_t hq_launch_compact(const hq_kargs &a, const hq_compact_bufs &b, uint3
     ++*launches;
   }
   return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------ compaction without any allocation
+// hpgq_compact_noalloc (include/hpg_fastq_cuda.h): the scan + copy kernels above with their scratch (the exclusive
+// scan of the per-read records and the block sums) in a file-scope device array instead of cudaMalloc'ed buffers,
+// for callers that may not allocate (CUDA graph capture, serving loops).  Every GPU that loads the library holds
+// the array (4 MB + 4 KB) until the process exits.
+namespace {
+constexpr uint32_t NOALLOC_SCAN = HPGQ_NOALLOC_MAX_READS + 2u;             // uint4 entries: scan[0..n]
+constexpr uint32_t NOALLOC_SUMS = (HPGQ_NOALLOC_MAX_READS + 1u) / 1024u + 2u;  // uint4 entries: block sums
+static __device__ __align__(256) uint4 g_noalloc_scratch[NOALLOC_SCAN + NOALLOC_SUMS];
+
+// In host code `g_noalloc_scratch` is only a stand-in for the symbol, not a device address: the address is asked for
+// once per device, with that device current, and cached.
+constexpr int NOALLOC_MAX_DEVICES = 64;
+uint4 *g_noalloc_ptr[NOALLOC_MAX_DEVICES];
+bool g_noalloc_have[NOALLOC_MAX_DEVICES];
+pthread_mutex_t g_noalloc_mu = PTHREAD_MUTEX_INITIALIZER;
+
+cudaError_t noalloc_scratch(int device, uint4 **out) {
+  cudaError_t e = cudaSuccess;
+  pthread_mutex_lock(&g_noalloc_mu);
+  if (!g_noalloc_have[device]) {
+    uint4 *p = nullptr;
+    e = cudaGetSymbolAddress((void **)&p, g_noalloc_scratch);
+    if (e == cudaSuccess) {
+      g_noalloc_ptr[device] = p;
+      g_noalloc_have[device] = true;
+    }
+  }
+  *out = g_noalloc_ptr[device];
+  pthread_mutex_unlock(&g_noalloc_mu);
+  return e;
+}
+}  // namespace
+
+extern "C" int hpgq_compact_noalloc(const uint8_t *d_seq, const uint8_t *d_qual, const uint32_t *d_idx,
+                                    const uint8_t *d_mask, const hpgq_trim_t *d_trim, uint32_t n_reads, uint32_t max_len,
+                                    uint8_t *d_out_seq, uint8_t *d_out_qual, uint32_t *d_out_idx, uint32_t *d_out_src,
+                                    uint32_t *d_totals, void *stream) {
+  if (!d_seq || !d_qual || !d_idx || !d_out_seq || !d_out_qual || !d_out_idx || !d_out_src || !d_totals)
+    return hq_fail_msg(HPGQ_ERR_INVALID, "compact_noalloc: null argument");
+  if (n_reads > HPGQ_NOALLOC_MAX_READS)
+    return hq_fail_msg(HPGQ_ERR_INVALID,
+                       "compact_noalloc: n_reads exceeds HPGQ_NOALLOC_MAX_READS (262144), the size of the library's static "
+                       "scratch; split the batch or use hpgq_batch_submit* with HPGQ_WORK_COMPACT");
+  int device = -1;
+  cudaError_t e = cudaGetDevice(&device);
+  if (e != cudaSuccess) return hq_fail_cuda(e, "compact_noalloc: cudaGetDevice");
+  if (device < 0 || device >= NOALLOC_MAX_DEVICES) return hq_fail_msg(HPGQ_ERR_INVALID, "compact_noalloc: device ordinal out of range");
+  uint4 *scratch = nullptr;
+  if ((e = noalloc_scratch(device, &scratch)) != cudaSuccess) return hq_fail_cuda(e, "compact_noalloc: cudaGetSymbolAddress");
+  hq_kargs a;
+  memset(&a, 0, sizeof a);
+  a.seq = d_seq;
+  a.qual = d_qual;
+  a.idx = d_idx;
+  a.n_reads = n_reads;
+  a.mask = const_cast<uint8_t *>(d_mask);
+  a.trim = const_cast<hpgq_trim_t *>(d_trim);
+  hq_compact_bufs b;
+  memset(&b, 0, sizeof b);
+  // Nothing in the scratch has to start at zero: the three scan kernels write block_sums[0, nb) and scan[0, n] before
+  // the copy kernel reads them, so what the previous call left behind is never read.
+  b.scan = scratch;
+  b.block_sums = scratch + NOALLOC_SCAN;
+  b.out_seq = d_out_seq;
+  b.out_qual = d_out_qual;
+  b.out_idx = d_out_idx;
+  b.out_src = d_out_src;
+  b.totals = d_totals;
+  uint64_t launches = 0;
+  // lanes per read of the generic copy kernel: from the longest read when the caller states it, else a whole warp
+  const uint32_t mean_len = max_len ? max_len : 401u;
+  e = hq_launch_compact(a, b, mean_len, max_len, static_cast<cudaStream_t>(stream), &launches);
+  if (e != cudaSuccess) return hq_fail_cuda(e, "compact_noalloc: kernel launch");
+  if (n_reads == 0) {  // the copy kernel, which closes out_idx with the total, does not run for an empty batch
+    e = cudaMemsetAsync(d_out_idx, 0, 4, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return hq_fail_cuda(e, "compact_noalloc: cudaMemsetAsync");
+  }
+  return HPGQ_OK;
 }

@@ -73,6 +73,10 @@ struct hq_compact_bufs {
   uint8_t *fail_seq, *fail_qual;
   uint32_t *fail_idx, *fail_src;
 };
+// error reporting of hpgq_api.cu (thread-local hpgq_last_error text) for entry points that live in other files
+int hq_fail_msg(int code, const char *what);
+int hq_fail_cuda(cudaError_t e, const char *what);
+
 // decisions (trim, filter) and compaction in one pass over the batch; false = this batch needs the two-pass path
 bool hq_fz_supports(uint32_t work, uint32_t max_len, uint32_t n_reads, const hq_compact_bufs &b);
 // decisions only (edit / filter without statistics), word frame; cudaErrorInvalidValue = use hq_launch_qc_group

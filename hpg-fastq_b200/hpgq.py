@@ -105,7 +105,7 @@ EXPORTS = [
     "hpgq_strerror", "hpgq_last_error", "hpgq_layout", "hpgq_device_count", "hpgq_ctx_create", "hpgq_ctx_destroy",
     "hpgq_set_params", "hpgq_get_layout", "hpgq_batch_submit", "hpgq_batch_submit_device", "hpgq_batch_wait",
     "hpgq_batch_submit_text", "hpgq_batch_submit_text_fd", "hpgq_batch_text_launch", "hpgq_batch_text_cancel", "hpgq_batch_text_headers",
-    "hpgq_batch_wait_text", "hpgq_batch_wait_text_fd", "hpgq_ctx_reserve_text", "hpgq_comm_prepare",
+    "hpgq_batch_wait_text", "hpgq_batch_wait_text_fd", "hpgq_ctx_reserve_text", "hpgq_comm_prepare", "hpgq_compact_noalloc",
     "hpgq_batch_sync", "hpgq_batch_device_views", "hpgq_batch_checksum", "hpgq_checksum_host", "hpgq_counters_reset", "hpgq_counters_download",
     "hpgq_counters_device_ptr", "hpgq_counters_reduce", "hpgq_counters_finalize_host", "hpgq_slot_stream", "hpgq_launch_count",
     "hpgq_last_kernel_ms", "hpgq_synth_device", "hpgq_synth_host", "hpgq_dev_alloc", "hpgq_dev_free",

@@ -268,6 +268,32 @@ int hpgq_batch_sync(hpgq_ctx_t *ctx, int slot);
 /* device views of the slot's outputs (mask / trim / compacted arrays), valid until resubmit */
 int hpgq_batch_device_views(hpgq_ctx_t *ctx, int slot, hpgq_batch_result_t *res);
 
+/* Compaction without any allocation.  This entry point has no counterpart in the reference; it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid it).  It is the order-preserving partition of HPGQ_WORK_COMPACT (passed
+ * reads, then failed reads, each in input order, trimmed to d_trim when given) on caller-owned device arrays: the same
+ * kernels, with their scratch (the exclusive scan of the per-read records, 16 bytes per read, and its block sums) in a
+ * static device array inside the library instead of buffers from cudaMalloc.  It calls no cudaMalloc / cudaFree and
+ * no allocating library routine, needs no ctx, and works on the device that is current on the calling thread (all
+ * pointers must belong to it).
+ *   inputs   d_seq, d_qual, d_idx[n_reads + 1]: the batch as in hpgq_batch_t (device pointers);
+ *            d_mask[n_reads]: 1 = passed, 0 = failed, NULL = every read passed;
+ *            d_trim[n_reads]: kept range of every read, NULL = whole reads;
+ *            max_len: 0, or a length no read exceeds (selects the staged copy kernel for reads up to 22 000 bases;
+ *            a value SMALLER than the longest read is a caller error with undefined output -- 0 is always safe);
+ *   outputs  d_out_seq, d_out_qual: (idx[n] - idx[0]) + 64 bytes each; d_out_idx[n_reads + 1]; d_out_src[n_reads];
+ *            d_totals[4] = passed reads, failed reads, passed bytes, failed bytes -- as hpgq_batch_result_t's views;
+ *   stream   a cudaStream_t (NULL = the legacy default stream); the call only enqueues, the caller synchronises.
+ * Limit: n_reads <= HPGQ_NOALLOC_MAX_READS; more is rejected with HPGQ_ERR_INVALID and a message.  The scratch array
+ * (4 MB + 4 KB) is held by every GPU that loads the library until the process exits.  ALL calls on a device share it:
+ * calls whose kernels may overlap on the GPU (different streams without an ordering between them, or two host threads)
+ * race and produce garbage -- order them on one stream or with events.  Nothing in it has to be zero at entry (every
+ * word a call reads it has written before), so the contents a previous call left behind do no harm. */
+#define HPGQ_NOALLOC_MAX_READS 262144u
+int hpgq_compact_noalloc(const uint8_t *d_seq, const uint8_t *d_qual, const uint32_t *d_idx, const uint8_t *d_mask,
+                         const hpgq_trim_t *d_trim, uint32_t n_reads, uint32_t max_len, uint8_t *d_out_seq,
+                         uint8_t *d_out_qual, uint32_t *d_out_idx, uint32_t *d_out_src, uint32_t *d_totals, void *stream);
+
 /* Order-sensitive 64-bit checksum of the compacted output (HPGQ_WORK_COMPACT) a slot holds, computed on the
  * device; the slot must be idle (after hpgq_batch_wait / hpgq_batch_sync).  hpgq_checksum_host is the same sum over
  * host arrays: sum of hpgq_checksum_mix(position, value) (include/hpgq_synth.h) over out_seq[0..T), out_qual[0..T) (positions T + i),
