@@ -67,6 +67,7 @@ struct hpgq_slot {
   // outputs
   uint8_t *d_mask = nullptr, *h_mask = nullptr;
   uint8_t *d_cgflag = nullptr;  // chaos game: reads to re-emulate in double arithmetic
+  uint32_t *d_rsum = nullptr;   // per-read sums of the one-pass statistics of long reads (zero between batches)
   hpgq_trim_t *d_trim = nullptr, *h_trim = nullptr;
   uint32_t *d_maxlen = nullptr, *h_small = nullptr; // h_small: [0..2]=max/min length, order flag [4..7]=totals [8..9]=HPGQ_S_BAD_BATCH (pinned)
   hq_compact_bufs cb = {};
@@ -208,6 +209,7 @@ static void slot_free(hpgq_slot &s) {
   cudaFreeHost(s.h_seq); cudaFreeHost(s.h_qual); cudaFreeHost(s.h_idx);
   cudaFree(s.d_mask); cudaFreeHost(s.h_mask);
   cudaFree(s.d_cgflag);
+  cudaFree(s.d_rsum);
   cudaFree(s.d_trim); cudaFreeHost(s.h_trim);
   cudaFree(s.d_maxlen); cudaFreeHost(s.h_small);
   cudaFree(s.cb.scan); cudaFree(s.cb.block_sums); cudaFree(s.cb.out_seq); cudaFree(s.cb.out_qual);

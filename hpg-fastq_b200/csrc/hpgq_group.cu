@@ -366,9 +366,9 @@ constexpr int POS_CH = POS_SLOT / 16;          // 16-byte chunks per slot
 
 struct pos_entry {
   uint32_t ga;     // batch offset of the 16-byte aligned superset of the tile's bytes of one read
-  uint32_t gb;     // its size in bytes (multiple of 16)
+  uint32_t gb;     // its size in bytes (multiple of 16, <= POS_SLOT) | offset of position p0 inside the superset << 16
   uint32_t L;      // read length
-  uint32_t delta;  // offset of position p0 inside the superset
+  uint32_t r;      // the read
 };
 constexpr int POS_FIFO = 128;  // descriptors; live range at any time < 4 * (NS + 2) + 32
 
@@ -397,13 +397,19 @@ __device__ __forceinline__ void lds8(const uint8_t *slot, uint32_t x, uint32_t &
   v1 = (uint32_t)(v >> 32);
 }
 
+// MODE 0: the reads the mask lets through (every read without a mask).
+// MODE 1: EVERY read, and the tile's share of each read's quality sum / G+C count / N count is added to a.rsum
+//         (two words per read) -- the decisions are made from those sums afterwards (hq_pos_finish_kernel), so that
+//         long reads are read once; MODE 2 then takes the reads that FAILED out of the tables again.
+// MODE 2: the reads with mask == 0, subtracted.
+template <int MODE>
 __global__ void __launch_bounds__(POS_THREADS, 2) hq_pos_kernel(hq_kargs a, uint32_t reads_per_slab) {
   extern __shared__ __align__(128) uint8_t pos_raw[];
   pos_smem &sm = *reinterpret_cast<pos_smem *>(pos_raw);
   const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
   const uint32_t p0 = blockIdx.x * POS_TILE;
   const uint32_t p = p0 + tid * POS_PER;
-  const bool use_mask = (a.work & HPGQ_WORK_FILTER) != 0 && a.mask != nullptr;
+  const bool use_mask = MODE == 0 && (a.work & HPGQ_WORK_FILTER) != 0 && a.mask != nullptr;
   if (tid == 0) {
     for (int s = 0; s < POS_NS; ++s) hq_mbar_init(&sm.full[s], POS_THREADS);
     hq_mbar_init_fence();
@@ -412,21 +418,30 @@ __global__ void __launch_bounds__(POS_THREADS, 2) hq_pos_kernel(hq_kargs a, uint
   if (tid == 0) sm.total = 0xFFFFFFFFu;
   // ---- warp 0: scan of the slab's reads, 32 per step; the lanes whose read covers the tile append its descriptor
   // to the FIFO at (appended + rank among the hits).  The idx / mask loads of the next step are already in flight.
+  // MODE 2 walks the list of failed reads hq_pos_finish_kernel has written (a.flist[0] entries from a.flist[1] on)
+  // instead of the batch: with few failures a CTA has next to nothing to scan
+  const uint32_t n_scan = MODE == 2 ? a.flist[0] : a.n_reads;
+  if (MODE == 2) {  // at least 64 reads per slab (the ring needs a few stages to hide its latency): the other CTAs leave
+    const uint32_t slabs = min(gridDim.y, max(1u, n_scan / 64u));
+    if (blockIdx.y >= slabs) return;
+    reads_per_slab = (n_scan + slabs - 1u) / slabs;
+  }
   uint32_t scan = blockIdx.y * reads_per_slab;
-  const uint32_t scan_end = min(a.n_reads, scan + reads_per_slab);
-  uint32_t appended = 0, po = 0, pe = 0, pm = 0;
+  const uint32_t scan_end = min(n_scan, scan + reads_per_slab);
+  uint32_t appended = 0, po = 0, pe = 0, pm = 0, pr = 0;
   bool exhausted = scan >= scan_end;
   auto prefetch = [&]() {
-    const uint32_t r = scan + lane;
-    const bool valid = r < scan_end;
-    po = valid ? a.idx[r] : 0u;
-    pe = valid ? a.idx[r + 1] : 0u;
-    pm = valid ? (use_mask ? (uint32_t)a.mask[r] : 1u) : 0u;
+    const uint32_t i = scan + lane;
+    const bool valid = i < scan_end;
+    pr = MODE == 2 ? (valid ? a.flist[1u + i] : 0u) : i;
+    po = valid ? a.idx[pr] : 0u;
+    pe = valid ? a.idx[pr + 1] : 0u;
+    pm = valid ? (use_mask ? (uint32_t)(a.mask[pr] != 0) : 1u) : 0u;
   };
   if (warp == 0 && !exhausted) prefetch();
   auto produce = [&](uint32_t need) {
     while (appended < need && !exhausted) {
-      const uint32_t o = po, L = pe - po;
+      const uint32_t o = po, L = pe - po, rd = pr;
       const bool ok = pm != 0u && L > p0 && L <= a.Lcap;
       scan += 32u;
       if (scan < scan_end) prefetch();
@@ -437,9 +452,9 @@ __global__ void __launch_bounds__(POS_THREADS, 2) hq_pos_kernel(hq_kargs a, uint
         const uint32_t last = o + min(L, p0 + (uint32_t)POS_TILE);
         pos_entry e;
         e.ga = ga;
-        e.gb = ((last - ga) + 15u) & ~15u;
+        e.gb = (((last - ga) + 15u) & ~15u) | ((first - ga) << 16);
         e.L = L;
-        e.delta = first - ga;
+        e.r = rd;
         sm.fifo[(appended + __popc(bal & ((1u << lane) - 1u))) % POS_FIFO] = e;
       }
       appended += __popc(bal);
@@ -455,11 +470,12 @@ __global__ void __launch_bounds__(POS_THREADS, 2) hq_pos_kernel(hq_kargs a, uint
       const uint32_t ei = POS_RB * j + k;
       if (ei < tot) {
         const pos_entry e = sm.fifo[ei % POS_FIFO];
+        const uint32_t gb = e.gb & 0xFFFFu;
         const uint8_t *gs = a.seq + e.ga, *gq = a.qual + e.ga;
         uint8_t *ds = sm.buf[s][k][0], *dq = sm.buf[s][k][1];
 #pragma unroll
         for (uint32_t off = 16u * lane; off < 16u * (uint32_t)POS_CH; off += 512u)
-          if (off < e.gb) {
+          if (off < gb) {
             hq_cp_async16(ds + off, gs + off);
             hq_cp_async16(dq + off, gq + off);
           }
@@ -477,6 +493,7 @@ __global__ void __launch_bounds__(POS_THREADS, 2) hq_pos_kernel(hq_kargs a, uint
   uint32_t q16[2][2] = {{0u, 0u}, {0u, 0u}};                               // 16-bit lanes: (byte0, byte2), (byte1, byte3)
   uint32_t nb[3][2] = {{0u, 0u}, {0u, 0u}, {0u, 0u}};  // 4-bit lanes (<= 15 reads): C | G << 4, A | T << 4, N
   uint32_t since = 0, nsince = 0;
+  uint32_t tv[MODE == 1 ? POS_RB : 1];  // MODE 1: the thread's share of the sums of the stage's reads
   auto fold_nibbles = [&]() {
 #pragma unroll
     for (int w = 0; w < 2; ++w) {
@@ -508,10 +525,12 @@ __global__ void __launch_bounds__(POS_THREADS, 2) hq_pos_kernel(hq_kargs a, uint
       const uint32_t ei = POS_RB * it + k;
       const pos_entry e = sm.fifo[ei % POS_FIFO];
       const uint32_t L = ei < tot ? e.L : 0u;
+      if (MODE == 1) tv[k] = 0u;
       if (p < L && !(a.work & 0x8000u)) {
         // 16 bytes around the thread's eight: the byte phase (delta & 7) is the same for every thread of the CTA, so
         // the funnel is a uniform choice of three words and one PRMT per output word
-        const uint32_t x = e.delta + tid * POS_PER, sh = e.delta & 7u;
+        const uint32_t delta = e.gb >> 16;
+        const uint32_t x = delta + tid * POS_PER, sh = delta & 7u;
         const uint2 *ws = reinterpret_cast<const uint2 *>(sm.buf[s][k][0] + (x & ~7u));
         const uint2 *wq = reinterpret_cast<const uint2 *>(sm.buf[s][k][1] + (x & ~7u));
         const uint2 s0 = ws[0], s1 = ws[1], q0 = wq[0], q1 = wq[1];
@@ -561,6 +580,30 @@ __global__ void __launch_bounds__(POS_THREADS, 2) hq_pos_kernel(hq_kargs a, uint
           nb[2][w] += nv;
           q16[0][w] += __byte_perm(qm, 0u, 0x4240u);
           q16[1][w] += __byte_perm(qm, 0u, 0x4341u);
+          // the thread's share of the read's sums: quality (8 bytes: < 2^11) | G+C count << 11 | N count << 20
+          if (MODE == 1) tv[k] = __dp4a(qm, 0x01010101u, tv[k]) + ((uint32_t)__popc(cgv) << 11) + ((uint32_t)__popc(nv) << 20);
+        }
+      }
+    }
+    if (MODE == 1) {
+      // after the stage's reads, so that the reductions overlap: a warp covers 256 positions, its counts are <= 256
+      // (9 bits each), its quality sum < 2^16.  Lane k keeps the sums of read k and adds them to the read's words.
+      uint32_t mq = 0u, mc = 0u;
+#pragma unroll
+      for (int k = 0; k < POS_RB; ++k) {
+        const uint32_t sq = __reduce_add_sync(0xFFFFFFFFu, tv[k] & 0x7FFu);
+        const uint32_t sc = __reduce_add_sync(0xFFFFFFFFu, tv[k] >> 11);
+        if (lane == (uint32_t)k) {
+          mq = sq;
+          mc = sc;
+        }
+      }
+      const uint32_t ei = POS_RB * it + lane;
+      if (lane < (uint32_t)POS_RB && ei < tot) {
+        const pos_entry e = sm.fifo[ei % POS_FIFO];
+        if (p0 + (warp << 8) < e.L) {
+          atomicAdd(&a.rsum[2u * e.r], mq);
+          atomicAdd(&a.rsum[2u * e.r + 1u], (mc & 0x1FFu) | ((mc >> 9) << 16));
         }
       }
     }
@@ -606,7 +649,75 @@ __global__ void __launch_bounds__(POS_THREADS, 2) hq_pos_kernel(hq_kargs a, uint
   for (int t = 0; t < 6; ++t)
 #pragma unroll
     for (int i = 0; i < POS_PER; ++i)
-      if (acc[t][i] && p + i < a.Lcap) atomicAdd(&C[sec[t] + p + i], (unsigned long long)acc[t][i]);
+      if (acc[t][i] && p + i < a.Lcap)
+        atomicAdd(&C[sec[t] + p + i], MODE == 2 ? 0ull - (unsigned long long)acc[t][i] : (unsigned long long)acc[t][i]);
+}
+
+// Decisions and per-read statistics from the sums hq_pos_kernel<1> has collected (one thread per read); the sums are
+// cleared for the next batch.  Same expressions as hq_qc_group_kernel; the options it cannot serve (out-of-quality
+// count, window means, trimming) never get here (hq_pos_fused_supports).
+__global__ void __launch_bounds__(256) hq_pos_finish_kernel(hq_kargs a, uint32_t stated_max_len) {
+  const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31u;
+  const bool do_filter = a.work & HPGQ_WORK_FILTER;
+  unsigned long long *C = a.ctr;
+  uint32_t n_pass = 0, n_fail = 0, n_stat = 0, qbin = 0, gbin = 0;
+  bool failed = false, hist = false;
+  unsigned long long acc_len = 0;
+  if (r < a.n_reads) {
+    const uint32_t len = a.idx[r + 1] - a.idx[r];
+    // a read longer than the caller said: its tail was not covered, the batch's results are void (HPGQ_ERR_INVALID at wait)
+    if (len > stated_max_len) atomicExch(&C[HPGQ_S_BAD_BATCH], 1ull);
+    const uint32_t S = a.rsum[2u * r], pk = a.rsum[2u * r + 1u];
+    a.rsum[2u * r] = 0u;
+    a.rsum[2u * r + 1u] = 0u;
+    const uint32_t nGC = pk & 0xFFFFu, nN = pk >> 16;
+    bool pass = true;
+    if (do_filter) {
+      pass = (long long)len >= a.min_len && (long long)len <= a.max_len && mean_ok_g(S, len, a.q_lo, a.q_hi) &&
+             (long long)nN <= a.max_n;
+      n_pass = pass;
+      n_fail = !pass;
+    }
+    if (a.mask) a.mask[r] = pass ? 1 : 0;
+    failed = !pass;
+    if (pass && len <= a.Lcap) {
+      n_stat = 1;
+      acc_len = len;
+      atomicAdd(&C[a.o_len_hist + len], 1ull);
+      atomicAdd(&C[a.o_sumq + len], (unsigned long long)S);
+      hist = len != 0u;
+      if (hist) {
+        qbin = (uint32_t)((2ull * S + len) / (2ull * len));
+        gbin = (uint32_t)((100ull * nGC) / len);
+      }
+    }
+  }
+  // the mean quality and the G+C percentage of a batch fall into a handful of bins: one atomic per bin and warp
+  const unsigned hm = __ballot_sync(0xFFFFFFFFu, hist);
+  if (hist) {
+    const unsigned mq_ = __match_any_sync(hm, qbin), mg_ = __match_any_sync(hm, gbin);
+    if (lane == (uint32_t)__ffs(mq_) - 1u) atomicAdd(&C[a.o_qual_hist + qbin], (unsigned long long)__popc(mq_));
+    if (lane == (uint32_t)__ffs(mg_) - 1u) atomicAdd(&C[a.o_gc_hist + gbin], (unsigned long long)__popc(mg_));
+  }
+  // the failed reads, for hq_pos_kernel<2> (any order: it subtracts sums)
+  const unsigned fm = __ballot_sync(0xFFFFFFFFu, failed);
+  if (fm && a.flist) {
+    uint32_t base = 0;
+    if (lane == (uint32_t)__ffs(fm) - 1u) base = atomicAdd(&a.flist[0], (uint32_t)__popc(fm));
+    base = __shfl_sync(0xFFFFFFFFu, base, __ffs(fm) - 1);
+    if (failed) a.flist[1u + base + __popc(fm & ((1u << lane) - 1u))] = r;
+  }
+  n_pass = group_sum<32>(n_pass);
+  n_fail = group_sum<32>(n_fail);
+  n_stat = group_sum<32>(n_stat);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc_len += __shfl_xor_sync(0xFFFFFFFFu, acc_len, o);
+  if (lane == 0) {
+    if (n_pass) atomicAdd(&C[HPGQ_S_NUM_PASSED], (unsigned long long)n_pass);
+    if (n_fail) atomicAdd(&C[HPGQ_S_NUM_FAILED], (unsigned long long)n_fail);
+    if (n_stat) atomicAdd(&C[HPGQ_S_NUM_READS], (unsigned long long)n_stat);
+    if (acc_len) atomicAdd(&C[HPGQ_S_ACC_LENGTH], acc_len);
+  }
 }
 
 }  // namespace
@@ -647,9 +758,9 @@ cudaError_t hq_launch_qc_group(const hq_kargs &a, uint32_t max_len_in_batch, int
   return cudaGetLastError();
 }
 
-cudaError_t hq_launch_pos(const hq_kargs &a, uint32_t max_len_in_batch, int sm_count, cudaStream_t st,
-                          uint64_t *launches) {
-  if (a.n_reads == 0 || max_len_in_batch == 0) return cudaSuccess;
+namespace {
+template <int MODE>
+cudaError_t launch_pos_mode(const hq_kargs &a, uint32_t max_len_in_batch, int sm_count, cudaStream_t st, uint64_t *launches) {
   const uint32_t cover = max_len_in_batch < a.Lcap ? max_len_in_batch : a.Lcap;
   const uint32_t tiles = (cover + POS_TILE - 1u) / POS_TILE;
   // 2 CTAs are resident per SM (67 KB ring each, <= 128 registers): four waves, the tiles near the longest reads
@@ -663,9 +774,47 @@ cudaError_t hq_launch_pos(const hq_kargs &a, uint32_t max_len_in_batch, int sm_c
   hq_kargs a2 = a;
   if (getenv("HPGQ_DEBUG_LOADONLY")) a2.work |= 0x8000u;  // developer probe: ring traffic without the arithmetic
   // per device, so set on every launch (one process may drive several GPUs)
-  cudaError_t e = cudaFuncSetAttribute(hq_pos_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(pos_smem));
+  cudaError_t e = cudaFuncSetAttribute(hq_pos_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(pos_smem));
   if (e != cudaSuccess) return e;
-  hq_pos_kernel<<<dim3(tiles, slabs), POS_THREADS, sizeof(pos_smem), st>>>(a2, reads_per_slab);
+  hq_pos_kernel<MODE><<<dim3(tiles, slabs), POS_THREADS, sizeof(pos_smem), st>>>(a2, reads_per_slab);
   ++*launches;
   return cudaGetLastError();
+}
+}  // namespace
+
+cudaError_t hq_launch_pos(const hq_kargs &a, uint32_t max_len_in_batch, int sm_count, cudaStream_t st,
+                          uint64_t *launches) {
+  if (a.n_reads == 0 || max_len_in_batch == 0) return cudaSuccess;
+  return launch_pos_mode<0>(a, max_len_in_batch, sm_count, st, launches);
+}
+
+// Statistics (+ filter) of long reads with ONE pass over the batch: per-position tables of every read and the per-read
+// sums (MODE 1), decisions and per-read histograms from the sums, then the failed reads are taken out of the tables
+// again (MODE 2 reads only those).  Exact: the tables are integer sums.  Needs the per-read counts to fit 16 bits, every
+// read inside the tables, and a filter made of length, mean quality and N count only.
+bool hq_pos_fused_supports(const hq_kargs &a, uint32_t max_len_in_batch) {
+  const bool off = getenv("HPGQ_NO_POSFUSE") != nullptr;  // developer A/B: decision kernel + masked position pass
+  if (off || !a.rsum || !a.flist || !(a.work & HPGQ_WORK_STATS) || (a.work & HPGQ_WORK_EDIT)) return false;
+  if (max_len_in_batch == 0 || max_len_in_batch > 65535u || max_len_in_batch > a.Lcap) return false;
+  if (a.work & HPGQ_WORK_FILTER) {
+    if (a.f_ll > 0 || a.f_rl > 0) return false;
+    if ((long long)a.max_ooq < (long long)max_len_in_batch) return false;  // some read could fail on its out-of-quality count
+    if (!a.mask) return false;
+  }
+  return true;
+}
+
+cudaError_t hq_launch_pos_fused(const hq_kargs &a, uint32_t max_len_in_batch, int sm_count, cudaStream_t st,
+                                uint64_t *launches) {
+  if (a.n_reads == 0) return cudaSuccess;
+  cudaError_t e = launch_pos_mode<1>(a, max_len_in_batch, sm_count, st, launches);
+  if (e != cudaSuccess) return e;
+  if (a.work & HPGQ_WORK_FILTER) {
+    if ((e = cudaMemsetAsync(a.flist, 0, 4, st)) != cudaSuccess) return e;
+  }
+  hq_pos_finish_kernel<<<(a.n_reads + 255u) / 256u, 256, 0, st>>>(a, max_len_in_batch);
+  ++*launches;
+  if ((e = cudaGetLastError()) != cudaSuccess) return e;
+  if (a.work & HPGQ_WORK_FILTER) e = launch_pos_mode<2>(a, max_len_in_batch, sm_count, st, launches);
+  return e;
 }

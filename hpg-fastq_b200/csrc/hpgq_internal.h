@@ -34,6 +34,8 @@ struct hq_kargs {
   uint8_t *mask;     // may be NULL
   hpgq_trim_t *trim; // may be NULL
   uint8_t *cgflag;   // chaos game: reads to re-emulate in double arithmetic (n_reads bytes), may be NULL
+  uint32_t *flist;   // one-pass statistics of long reads: [0] = number of failed reads, then their indices (n_reads + 1 words)
+  uint32_t *rsum;    // one-pass statistics of long reads: quality sum, G+C | N << 16 per read (all zero between batches), may be NULL
   // tiled-kernel geometry
   uint32_t RT;          // reads per tile (multiple of 4)
   uint32_t G;           // lanes per read group
@@ -56,6 +58,10 @@ cudaError_t hq_launch_qc_group(const hq_kargs &a, uint32_t max_len_in_batch, int
                                uint64_t *launches);
 cudaError_t hq_launch_pos(const hq_kargs &a, uint32_t max_len_in_batch, int sm_count, cudaStream_t st,
                           uint64_t *launches);
+// statistics (+ simple filter) of long reads in one pass over the batch (hpgq_group.cu); false = decision kernel + hq_launch_pos
+bool hq_pos_fused_supports(const hq_kargs &a, uint32_t max_len_in_batch);
+cudaError_t hq_launch_pos_fused(const hq_kargs &a, uint32_t max_len_in_batch, int sm_count, cudaStream_t st,
+                                uint64_t *launches);
 cudaError_t hq_launch_kmers_cg(const hq_kargs &a, uint32_t max_len_in_batch, cudaStream_t st, uint64_t *launches);
 // d_out[0] = longest read, d_out[1] = shortest read, d_out[2] = 1 if some offset decreases
 cudaError_t hq_launch_maxlen(const uint32_t *idx, uint32_t n, uint32_t *d_out, cudaStream_t st, uint64_t *launches);

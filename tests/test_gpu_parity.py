@@ -621,3 +621,51 @@ def test_out_of_quality_count_ignores_the_neighbouring_read(q, ob):
     par = q.make_params(q.WORK_STATS | q.WORK_FILTER, filter=dict(min_read_quality=10, max_read_quality=36, max_out_of_quality=128))
     _, _, _, emask, _ = check(q, ob, par, seq, qual, idx, 1536)
     assert 0 < int(emask.sum()) < len(emask)
+
+
+@pytest.mark.parametrize("two_pass", [False, True], ids=["one_pass", "two_pass"])
+def test_long_reads_statistics_in_one_pass(q, ob, two_pass):
+    """Statistics + a filter on length / mean quality / N count of reads too long for the tiled kernel: one pass over the
+    batch (position tables of every read + per-read sums, decisions from the sums, failed reads subtracted again) against
+    the oracle, and the two-pass path (HPGQ_NO_POSFUSE=1: decision kernel, masked position pass) on the same batches.
+    Filters that fail most reads, none, and all of them; three batches on two slots, so that the per-read sums left
+    behind by one batch would show in the next; a max-length statement the batch breaks."""
+    env = dict(HPGQ_NO_POSFUSE="1") if two_pass else {}
+    with _env(**env):
+        rng = np.random.default_rng(19)
+        seq, qual, idx = rand_batch(rng, 2500, 700, 9000, p_n=0.02)
+        for flt in (dict(min_read_length=3000, min_read_quality=37, max_N=90),   # most reads fail
+                    dict(min_read_length=1),                                       # none fails
+                    dict(min_read_length=100000),                                  # all fail
+                    dict(max_read_length=5000, max_read_quality=36, max_N=60)):
+            par = q.make_params(q.WORK_STATS | q.WORK_FILTER, filter=flt)
+            _, _, _, emask, _ = check(q, ob, par, seq, qual, idx, 9024)
+        assert int(emask.sum()) not in (0, len(emask))
+        check(q, ob, q.make_params(q.WORK_STATS), seq, qual, idx, 9024)
+        # batches of different sizes through the same slots: counters accumulate, the per-read sums start from zero
+        par = q.make_params(q.WORK_STATS | q.WORK_FILTER, filter=dict(min_read_length=2000, min_read_quality=36, max_N=70))
+        batches = [rand_batch(rng, n, 650, hi, p_n=0.02) for n, hi in ((1200, 6000), (300, 9000), (900, 3000))]
+        with q.Ctx(0, max_reads=1200, max_bytes=max(int(b[2][-1]) for b in batches) + 64, max_read_len=9024) as ctx:
+            ctx.set_params(par)
+            lay = ctx.layout
+            exp = np.zeros(lay.words, dtype=np.uint64)
+            got_masks, exp_masks = {}, {}
+            for k, (s_, q_, i_) in enumerate(batches):
+                if k >= 2:
+                    got_masks[k - 2] = ctx.wait(k & 1)["mask"]
+                ctx.submit(s_, q_, i_, k & 1)
+                exp, exp_masks[k], _ = ob.process_batch(par, lay, s_, q_, i_, counters=exp, finalize=False)
+            got_masks[1] = ctx.wait(1)["mask"]
+            got_masks[2] = ctx.wait(0)["mask"]
+            got = ctx.counters()
+        ob.lib().oracle_finalize(__import__("ctypes").byref(lay), exp.ctypes.data_as(__import__("ctypes").c_void_p))
+        for k in range(3):
+            assert np.array_equal(got_masks[k], exp_masks[k]), k
+        msg = diff_report(q, lay, got, exp)
+        assert not msg, msg
+        # a read longer than the stated maximum: refused, not silently short of its tail
+        seq, qual, idx = rand_batch(rng, 400, 700, 8000, p_n=0.01)
+        if not two_pass:
+            with pytest.raises(q.HpgqError, match="length statement"):
+                _device_check(q, ob, par, seq, qual, idx, 9024, hint=4096)
+        _device_check(q, ob, par, seq, qual, idx, 9024, hint=8000)
