@@ -248,6 +248,11 @@ __device__ __forceinline__ uint4 range_mask16(uint32_t lo, uint32_t hi) {
 
 __host__ __device__ constexpr uint32_t ct_rmap_bytes(uint32_t cap) { return ((cap >> 4) + 8u + 15u) & ~15u; }
 
+__device__ __forceinline__ void fz_cp16(void *dst_smem, const void *src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst_smem)), "l"(src)
+               : "memory");
+}
+
 // Builds the aligned 16-byte chunks of a tile's two output spans (stream 0 = passed, 1 = failed) from the staged
 // source bytes and stores them to oseq[stream] / oqual[stream]; h.key[stream][r] is the offset of read r inside that
 // stream's buffer, rmap the chunk -> read map (failed span's entries mo_f behind the passed span's).
@@ -257,6 +262,9 @@ __device__ __forceinline__ void ct_emit(const ct_hdr &h, const uint8_t *rmap, ui
 #pragma unroll 1
   for (int stream = 0; stream < 2; ++stream) {
     const uint32_t *key = h.key[stream];
+    // selected here, in registers: indexing the two-entry pointer arrays with the loop variable put them in local
+    // memory and a dependent LDL in front of every store (18 % of the stall samples of the gather kernel)
+    uint8_t *const os = stream ? oseq[1] : oseq[0], *const oq = stream ? oqual[1] : oqual[0];
     const uint32_t D0 = key[0], D1 = key[nt];
     if (D1 == D0) continue;
     // a warp owns a contiguous run of the span's chunks, so the read index only moves forward between its rounds
@@ -325,8 +333,8 @@ __device__ __forceinline__ void ct_emit(const ct_hdr &h, const uint8_t *rmap, ui
         }
       }
       if (d1 - d0 == 16u) {
-        *reinterpret_cast<uint4 *>(oseq[stream] + dc) = vs;
-        *reinterpret_cast<uint4 *>(oqual[stream] + dc) = vq;
+        *reinterpret_cast<uint4 *>(os + dc) = vs;
+        *reinterpret_cast<uint4 *>(oq + dc) = vq;
       } else {  // first / last chunk of the span: its other bytes belong to a neighbouring tile
         const uint32_t ws[4] = {vs.x, vs.y, vs.z, vs.w}, wq[4] = {vq.x, vq.y, vq.z, vq.w};
         const uint32_t vlo = d0 - dc, vhi = d1 - dc;
@@ -334,14 +342,14 @@ __device__ __forceinline__ void ct_emit(const ct_hdr &h, const uint8_t *rmap, ui
         for (int w = 0; w < 4; ++w) {
           const uint32_t w0 = 4u * w;
           if (vlo <= w0 && vhi >= w0 + 4u) {
-            *reinterpret_cast<uint32_t *>(oseq[stream] + dc + w0) = ws[w];
-            *reinterpret_cast<uint32_t *>(oqual[stream] + dc + w0) = wq[w];
+            *reinterpret_cast<uint32_t *>(os + dc + w0) = ws[w];
+            *reinterpret_cast<uint32_t *>(oq + dc + w0) = wq[w];
           } else if (vlo < w0 + 4u && vhi > w0) {
 #pragma unroll
             for (int t = 0; t < 4; ++t)
               if (w0 + t >= vlo && w0 + t < vhi) {
-                oseq[stream][dc + w0 + t] = (uint8_t)(ws[w] >> (8 * t));
-                oqual[stream][dc + w0 + t] = (uint8_t)(wq[w] >> (8 * t));
+                os[dc + w0 + t] = (uint8_t)(ws[w] >> (8 * t));
+                oq[dc + w0 + t] = (uint8_t)(wq[w] >> (8 * t));
               }
           }
         }
@@ -400,6 +408,118 @@ __global__ void __launch_bounds__(256) hq_compact_copy_tile(hq_kargs a, hq_compa
   if (blockIdx.x == 0 && tid == 0) b.out_idx[n] = tot.x + tot.y;
 }
 
+// The same with two tile buffers per CTA and NO synchronous global load on a tile's path.  The single-buffer kernel
+// pays, per tile, three dependent round trips to global memory (tile offsets -> scan / mask / trim records -> staged
+// span), ~2 us each under load, before it can build a chunk: 12.7 stall cycles per issued instruction on global loads,
+// issue slots 32 % busy (profiles/compact_r2_summary.md).  Here everything tile t + 1 needs -- its scan records, offsets,
+// mask bytes, trim records and its source span -- is sent to shared memory with cp.async while tile t is being built,
+// and the two offsets that size the copies of tile t + 2 are loaded into registers one iteration ahead.
+struct ct_raw_t {
+  uint4 scan[CT_RPT / 2 + 2];
+  uint32_t idx[CT_RPT / 2 + 4];
+  hpgq_trim_t trim[CT_RPT / 2];
+  uint32_t mask[CT_RPT / 8 + 2];  // the aligned words that hold the tile's mask bytes
+};
+
+__device__ __forceinline__ void ct_cp(void *dst_smem, const void *src, int bytes) {
+  const uint32_t d = (uint32_t)__cvta_generic_to_shared(dst_smem);
+  if (bytes == 4) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(src) : "memory");
+  else asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d), "l"(src) : "memory");
+}
+
+__global__ void __launch_bounds__(256) hq_compact_copy_tile2(hq_kargs a, hq_compact_bufs b, uint32_t rpt, uint32_t cap) {
+  extern __shared__ __align__(16) uint8_t ct_raw[];
+  constexpr uint32_t HDR = (sizeof(ct_hdr) + 15u) & ~15u, RAW = (sizeof(ct_raw_t) + 15u) & ~15u;
+  const uint32_t bufsz = RAW + ct_rmap_bytes(cap) + 2u * cap;  // a multiple of 16; the header is shared by both buffers
+  ct_hdr &h = *reinterpret_cast<ct_hdr *>(ct_raw);
+  const uint32_t tid = threadIdx.x, n = a.n_reads;
+  const uint4 tot = b.scan[n];
+  // copies of tile [i0, i1) into buffer k; s0 / s1 = idx[i0] / idx[i1]
+  auto send = [&](uint32_t i0, uint32_t k, uint32_t s0, uint32_t s1) {
+    uint8_t *base = ct_raw + HDR + k * bufsz;
+    ct_raw_t &w = *reinterpret_cast<ct_raw_t *>(base);
+    uint8_t *sseq = base + RAW + ct_rmap_bytes(cap), *squal = sseq + cap;
+    const uint32_t nt = min(n, i0 + rpt) - i0;
+    if (tid <= nt) {
+      fz_cp16(&w.scan[tid], &b.scan[i0 + tid]);
+      ct_cp(&w.idx[tid], &a.idx[i0 + tid], 4);
+      if (tid < nt && a.trim) ct_cp(&w.trim[tid], &a.trim[i0 + tid], 8);
+    }
+    if (a.mask && tid >= 128u) {
+      const uint8_t *m0 = a.mask + i0;
+      const uint8_t *ma = m0 - ((uintptr_t)m0 & 3u);
+      const uint32_t words = ((uint32_t)(m0 - ma) + nt + 3u) >> 2, t = tid - 128u;
+      if (t < words) ct_cp(&w.mask[t], ma + 4u * t, 4);
+    }
+    const uint32_t S0a = s0 & ~15u, nb16 = (s1 - S0a + 15u) >> 4;
+    for (uint32_t c = tid; c < nb16; c += 256u) {
+      fz_cp16(sseq + CT_PAD + 16u * c, a.seq + S0a + 16u * c);
+      fz_cp16(squal + CT_PAD + 16u * c, a.qual + S0a + 16u * c);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  const uint32_t step = gridDim.x * rpt;
+  uint32_t i0 = blockIdx.x * rpt, k = 0;
+  uint32_t n0 = 0, n1 = 0;  // idx[i0 + step], idx[min(n, i0 + step + rpt)]: loaded one iteration before they are used
+  if (i0 < n) {
+    send(i0, 0, a.idx[i0], a.idx[min(n, i0 + rpt)]);
+    if (i0 + step < n) {
+      n0 = a.idx[i0 + step];
+      n1 = a.idx[min(n, i0 + step + rpt)];
+    }
+  }
+  for (; i0 < n; i0 += step, k ^= 1u) {
+    const bool more = i0 + step < n;
+    if (more) {
+      send(i0 + step, k ^ 1u, n0, n1);  // its buffer was released by the barrier that closed tile t - 1
+      if (i0 + 2u * step < n) {
+        n0 = a.idx[i0 + 2u * step];
+        n1 = a.idx[min(n, i0 + 2u * step + rpt)];
+      }
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+    } else {
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+    }
+    __syncthreads();  // tile t's records and bytes have landed
+    uint8_t *base = ct_raw + HDR + k * bufsz;
+    const ct_raw_t &w = *reinterpret_cast<const ct_raw_t *>(base);
+    uint8_t *rmap = base + RAW;
+    const uint8_t *sseq = rmap + ct_rmap_bytes(cap), *squal = sseq + cap;
+    const uint32_t nt = min(n, i0 + rpt) - i0;
+    const uint4 sc0 = w.scan[0], sc1 = w.scan[nt];
+    const uint32_t mo_f = ((sc1.x + 15u) >> 4) - (sc0.x >> 4) + 1u;  // the failed span's chunks follow the passed span's
+    if (tid <= nt) {
+      const uint32_t r = tid, i = i0 + r;
+      const uint4 sc = w.scan[r];
+      h.key[0][r] = sc.x;
+      h.key[1][r] = tot.x + sc.y;
+      if (r < nt) {
+        const uint32_t mb = (uint32_t)((uintptr_t)(a.mask + i0) & 3u) + r;
+        const bool pass = a.mask ? ((w.mask[mb >> 2] >> (8u * (mb & 3u))) & 0xFFu) != 0u : true;
+        const uint32_t st = a.trim ? w.trim[r].start : 0u;
+        const uint32_t slot = pass ? sc.z : tot.z + sc.w;
+        b.out_src[slot] = i;
+        b.out_idx[slot] = pass ? sc.x : tot.x + sc.y;
+        h.soff[r] = w.idx[r] + st - (w.idx[0] & ~15u) + CT_PAD;
+        const uint4 scn = w.scan[r + 1u];
+        const uint32_t k0 = pass ? sc.x : tot.x + sc.y, k1 = pass ? scn.x : tot.x + scn.y;
+        const uint32_t D0s = pass ? sc0.x : tot.x + sc0.y;
+        if (k1 > k0) {
+          const uint32_t cb = D0s >> 4;
+          const uint32_t cf = k0 == D0s ? cb : (k0 + 15u) >> 4, cl = (k1 - 1u) >> 4;
+          uint8_t *mp = rmap + (pass ? 0u : mo_f) - cb;
+          for (uint32_t c = cf; c <= cl; ++c) mp[c] = (uint8_t)r;
+        }
+      }
+    }
+    __syncthreads();  // header and chunk map of tile t
+    uint8_t *const oseq[2] = {b.out_seq, b.out_seq}, *const oqual[2] = {b.out_qual, b.out_qual};
+    ct_emit(h, rmap, mo_f, sseq, squal, nt, oseq, oqual);
+    __syncthreads();  // tile t's buffer and the header are free again
+  }
+  if (blockIdx.x == 0 && tid == 0) b.out_idx[n] = tot.x + tot.y;
+}
+
 // ---------------------------------------------------------------- edit + filter + compaction in ONE pass over HBM
 // fastq_edit_worker / fastq_filter_worker (src/edit_fastq.c:142-178, src/filter_fastq.c:134-155) and the consumers'
 // fastq_fwrite of the passed / failed lists (src/edit_fastq.c:184-206, src/filter_fastq.c:161-174) for one batch.
@@ -411,10 +531,6 @@ __global__ void __launch_bounds__(256) hq_compact_copy_tile(hq_kargs a, hq_compa
 // straight to their final place, those of the failed span to a side buffer, because the failed reads follow ALL
 // passed reads of the batch and that total is only known at the end: hq_fz_finish moves the side buffer (a few
 // per cent of the bytes) behind the passed reads.  DRAM traffic: 2 L + 4 in, 2 L' + 17 out per read.
-__device__ __forceinline__ void fz_cp16(void *dst_smem, const void *src) {
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst_smem)), "l"(src)
-               : "memory");
-}
 // Look-back records.  A tile publishes its own totals and, once it knows them, the totals of everything up to and
 // including itself, each as four 64-bit words {value, 1}: a word is written once and carries its own validity, so
 // neither side needs a memory fence (a __threadfence here waits for the CTA's output stores: 40 % of the kernel).
@@ -1051,6 +1167,20 @@ cudaError_t hq_launch_compact(const hq_kargs &a, const hq_compact_bufs &b, uint3
       const uint32_t smem = (((uint32_t)sizeof(ct_hdr) + 15u) & ~15u) + ct_rmap_bytes(cap) + 2u * cap;
       uint32_t tiles = (a.n_reads + rpt - 1u) / rpt;
       if (tiles > 148u * 8u) tiles = 148u * 8u;
+      // two buffers of half-size tiles when at least two such tiles per CTA exist (HPGQ_CT_SINGLE: developer A/B)
+      const uint32_t rpt2 = rpt >= 32u ? rpt / 2u : 0u;
+      if (rpt2 && !getenv("HPGQ_CT_SINGLE")) {
+        const uint32_t cap2 = ((rpt2 * max_len + 15u) & ~15u) + 64u;
+        const uint32_t smem2 = (((uint32_t)sizeof(ct_hdr) + 15u) & ~15u) +
+                               2u * ((((uint32_t)sizeof(ct_raw_t) + 15u) & ~15u) + ct_rmap_bytes(cap2) + 2u * cap2);
+        uint32_t tiles2 = (a.n_reads + rpt2 - 1u) / rpt2;
+        if (tiles2 > 148u * 5u) tiles2 = 148u * 5u;
+        if (smem2 <= 48u * 1024u) {
+          hq_compact_copy_tile2<<<tiles2, 256, smem2, st>>>(a, b, rpt2, cap2);
+          ++*launches;
+          return cudaGetLastError();
+        }
+      }
       hq_compact_copy_tile<<<tiles, 256, smem, st>>>(a, b, rpt, cap);
       ++*launches;
       return cudaGetLastError();
