@@ -924,7 +924,7 @@ __global__ void __launch_bounds__(256, 4) hq_fz_kernel(hq_kargs a, hq_compact_bu
 // word; a group's loads cover consecutive 32-byte sectors).  ~ 40 instructions per read against ~ 100 for the
 // register-resident kernel of hpgq_group.cu, which remains for filter windows / out-of-quality limits / longer reads.
 template <int G>
-__global__ void __launch_bounds__(256) hq_dec_fast_kernel(hq_kargs a) {
+__global__ void __launch_bounds__(256, 4) hq_dec_fast_kernel(hq_kargs a) {
   constexpr int K = 5;
   constexpr uint32_t NG = 32u / G;
   const uint32_t lane = threadIdx.x & 31u, lig = lane % G, giw = lane / G;
@@ -936,10 +936,34 @@ __global__ void __launch_bounds__(256) hq_dec_fast_kernel(hq_kargs a) {
   lc.wl = lc.wr = 0u;
   const uint32_t end_ok = a.idx[a.n_reads] + 32u;
   const uint32_t *dummy = reinterpret_cast<const uint32_t *>(a.ctr);  // >= 32 u64 scalars + histograms: always readable
+  // the offsets of a round are loaded one round ahead, and the lines of its frames are asked for (prefetch into L1) as
+  // soon as the offsets are there: the round's own loads then hit L1 instead of waiting for HBM behind the offset load
+  // (45 % of the stall samples sat on that chain: profiles/compact_r2_summary.md)
+  uint32_t po = 0, pe = 0;
+  {
+    const uint32_t r = warp * NG + giw;
+    if (r < a.n_reads) {
+      po = a.idx[r];
+      pe = a.idx[r + 1];
+    }
+  }
   for (uint32_t r0 = warp * NG; r0 < a.n_reads; r0 += nwarps * NG) {  // warp-uniform trip count (shuffles below)
     const uint32_t r = r0 + giw;
     const bool live = r < a.n_reads;
-    const uint32_t o = live ? a.idx[r] : a.idx[0], L = live ? a.idx[r + 1] - o : 0u;
+    const uint32_t o = live ? po : a.idx[0], L = live ? pe - po : 0u;
+    {
+      const uint32_t rn = r + nwarps * NG;
+      if (rn < a.n_reads) {
+        po = a.idx[rn];
+        pe = a.idx[rn + 1];
+        // 32 bytes per lane of the group cover the frame (4 K G bytes + the phase) of the next read
+        const uint32_t off = (po & ~31u) + 32u * lig;
+        if (off < pe + 32u && off + 32u <= end_ok) {
+          asm volatile("prefetch.global.L1 [%0];" ::"l"(a.seq + off));
+          asm volatile("prefetch.global.L1 [%0];" ::"l"(a.qual + off));
+        }
+      }
+    }
     if (L != lc.L) fz_len_update<K, G>(a, lc, L, lig);
     // the frame of the last reads of the batch reaches past the arrays' readable end (idx[n] + 32): those reads take
     // the register code, whose loads stop at the read's end, and the frame loads of their lanes go to the counter block
