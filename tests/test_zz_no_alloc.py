@@ -42,13 +42,13 @@ class DevBuf:
         self.ctx.dev_free(self.ptr)
 
 
-def call_noalloc(q, ctx, seq, qual, idx, mask, trim, max_len, poison):
+def call_noalloc(q, ctx, seq, qual, idx, mask, trim, max_len, poison, mask_shift=0):
     """One call of the new entry point on the ctx's device, default stream; returns the downloaded outputs."""
     lib = q.load_library()
     n = len(idx) - 1
     nbytes = int(idx[-1]) - int(idx[0])
     bufs = dict(seq=DevBuf(ctx, seq.nbytes + 64, seq), qual=DevBuf(ctx, qual.nbytes + 64, qual), idx=DevBuf(ctx, idx.nbytes, idx),
-                mask=DevBuf(ctx, n, mask) if mask is not None else None,
+                mask=DevBuf(ctx, n + 8, np.concatenate([np.zeros(mask_shift, np.uint8), mask])) if mask is not None else None,
                 trim=DevBuf(ctx, 8 * n, trim.astype(np.uint32)) if trim is not None else None)
     fill = np.full(nbytes + 64, poison, dtype=np.uint8)
     out = dict(seq=DevBuf(ctx, nbytes + 64, fill), qual=DevBuf(ctx, nbytes + 64, fill),
@@ -57,7 +57,8 @@ def call_noalloc(q, ctx, seq, qual, idx, mask, trim, max_len, poison):
                tot=DevBuf(ctx, 16, np.full(4, 0xDEADBEEF, dtype=np.uint32)))
     try:
         p = lambda b: C.c_void_p(b.ptr if b is not None else None)
-        rc = lib.hpgq_compact_noalloc(p(bufs["seq"]), p(bufs["qual"]), p(bufs["idx"]), p(bufs["mask"]), p(bufs["trim"]),
+        pm = C.c_void_p(bufs["mask"].ptr + mask_shift if bufs["mask"] is not None else None)  # any byte alignment
+        rc = lib.hpgq_compact_noalloc(p(bufs["seq"]), p(bufs["qual"]), p(bufs["idx"]), pm, p(bufs["trim"]),
                                       C.c_uint32(n), C.c_uint32(max_len), p(out["seq"]), p(out["qual"]), p(out["idx"]),
                                       p(out["src"]), p(out["tot"]), C.c_void_p(None))
         assert rc == 0, lib.hpgq_last_error()
@@ -101,6 +102,9 @@ def test_compact_noalloc_equals_the_existing_entry_point(q):
         ref = existing_path(q, ctx, q.WORK_EDIT | q.WORK_FILTER | q.WORK_COMPACT, seq, qual, idx)
         for poison in (0x11, 0xEE):
             same(ref, call_noalloc(q, ctx, seq, qual, idx, ref["mask"], ref["trim"], 0, poison), len(idx) - 1)
+        # a mask that starts at an odd address (the staged kernel copies the mask in aligned words)
+        for shift in (1, 2, 3):
+            same(ref, call_noalloc(q, ctx, seq, qual, idx, ref["mask"], ref["trim"], 400, 0x77, mask_shift=shift), len(idx) - 1)
         # an empty batch
         e = np.zeros(0, dtype=np.uint8)
         got = call_noalloc(q, ctx, e, e, np.zeros(1, dtype=np.uint32), None, None, 0, 0x33)
