@@ -129,16 +129,22 @@ __global__ void __launch_bounds__(256) hq_qc_simple_kernel(hq_kargs a) {
 // k-mer ids: A=0 C=1 G=2 T=3, first base most significant, windows with any other byte skipped
 // (SURVEY.md 8c(5)); chaos game = integer-index form of old/chaos_game.c:165-267.
 constexpr uint32_t HQ_LOOKBACK = 20;
+// packed (count, quality sum) cells: count << 37 | sum.  A sub-launch covers < 2^27 words of < 2^10 each, so neither
+// field can overflow (2 x 27 + 10 = 64 bits); with 12-bit words the bound was 2^26 and a 2 M x 250 bp batch took eight
+// sub-launches, each followed by an unpack pass over the 32 MB table, instead of four
+constexpr int HQ_PK_SHIFT = 37;
+constexpr uint32_t HQ_PK_QMAX = 1024u;
+constexpr unsigned long long HQ_PK_WORDS = 1ull << 27;
 
 // One chaos-game word: table_seq[cell]++ and table_q[cell] += qval (old/chaos_game.c:253-259).  With a packed
-// shadow table both land in ONE 64-bit reduction, count in the top 26 bits and the quality sum in the low 38
-// (a sub-launch covers < 2^26 words and qval < 2^12, so neither field can overflow); hq_cg_unpack_kernel adds the
-// fields to the real tables afterwards.  Values outside [0, 4096) (qualities below the base quality wrap, as the
+// shadow table both land in ONE 64-bit reduction, count in the top 27 bits and the quality sum in the low 37
+// (a sub-launch covers < 2^27 words and qval < 2^10, so neither field can overflow); hq_cg_unpack_kernel adds the
+// fields to the real tables afterwards.  Values outside [0, 1024) (qualities below the base quality wrap, as the
 // reference's unsigned arithmetic does) go to the real tables directly.
 __device__ __forceinline__ void cg_add(const hq_kargs &a, uint64_t cell, uint32_t qval) {
   unsigned long long *C = a.ctr;
-  if (a.cg_pack && qval < 4096u) {
-    atomicAdd(&a.cg_pack[cell], (1ull << 38) | (unsigned long long)qval);
+  if (a.cg_pack && qval < HQ_PK_QMAX) {
+    atomicAdd(&a.cg_pack[cell], (1ull << HQ_PK_SHIFT) | (unsigned long long)qval);
   } else {
     atomicAdd(&C[a.o_cg_seq + cell], 1ull);
     atomicAdd(&C[a.o_cg_q + cell], (unsigned long long)qval);
@@ -150,15 +156,15 @@ __global__ void __launch_bounds__(256) hq_cg_unpack_kernel(hq_kargs a, uint32_t 
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < cells; i += gridDim.x * blockDim.x) {
     const unsigned long long v = a.cg_pack[i];
     if (v) {
-      C[a.o_cg_seq + i] += v >> 38;
-      C[a.o_cg_q + i] += v & ((1ull << 38) - 1ull);
+      C[a.o_cg_seq + i] += v >> HQ_PK_SHIFT;
+      C[a.o_cg_q + i] += v & ((1ull << HQ_PK_SHIFT) - 1ull);
       a.cg_pack[i] = 0ull;
     }
   }
 }
 
 // Packed k2-mer / chaos-game table -> K2, CG_SEQ, CG_Q.  Cell c (a k2-mer, first base most significant) holds
-// count << 38 | quality sum of the words that ended with it; the chaos-game cell of those words is
+// count << 37 | quality sum of the words that ended with it; the chaos-game cell of those words is
 // co_x = sum xbit(base_i) 2^i, co_y = sum ybit(base_i) 2^i over the last cg_k bases, oldest = bit 0
 // (old/chaos_game.c:200-228: A, T move x up; G, T move y up).
 __global__ void __launch_bounds__(256) hq_kc_unpack_kernel(hq_kargs a, uint32_t cells) {
@@ -173,9 +179,9 @@ __global__ void __launch_bounds__(256) hq_kc_unpack_kernel(hq_kargs a, uint32_t 
       const unsigned long long v = a.kc_pack[code];
       if (!v) continue;
       a.kc_pack[code] = 0ull;
-      C[a.o_k2 + code] += v >> 38;
-      cnt += v >> 38;
-      qs += v & ((1ull << 38) - 1ull);
+      C[a.o_k2 + code] += v >> HQ_PK_SHIFT;
+      cnt += v >> HQ_PK_SHIFT;
+      qs += v & ((1ull << HQ_PK_SHIFT) - 1ull);
     }
     if (!cnt) continue;
     uint32_t ix = 0, iy = 0;
@@ -272,14 +278,14 @@ __global__ void __launch_bounds__(256) hq_kmers_cg_kernel(hq_kargs a) {
         if (b >= 0) {
           // One 64-bit RED per base when k-mers and chaos game run together: the chaos-game cell of a word is a bit
           // permutation of the low 2 cg_k bits of the k2-mer that ends at the same base, so the k2-mer count and the
-          // word's quality sum travel as (1 << 38 | qsum) into ONE packed table indexed by the k2-mer;
+          // word's quality sum travel as (1 << 37 | qsum) into ONE packed table indexed by the k2-mer;
           // hq_kc_unpack_kernel splits it into K2, CG_SEQ and CG_Q.  The two tables were 2 REDs per base, and the
           // kernel runs at the L2 atomic rate (~189 G RED/s).
           const uint32_t qval = accq - (uint32_t)(a.cg_base_quality * ck);
           const bool kev = kmers_here && k2 > 0 && valid >= (uint32_t)k2;
           const bool cev = do_cg && !other && cnt >= (uint32_t)ck;
-          if (merged && kev && cev && qval < 4096u) {
-            atomicAdd(&a.kc_pack[code & k2mask], (1ull << 38) | (unsigned long long)qval);
+          if (merged && kev && cev && qval < HQ_PK_QMAX) {
+            atomicAdd(&a.kc_pack[code & k2mask], (1ull << HQ_PK_SHIFT) | (unsigned long long)qval);
             words++;
           } else {
             // 5-mer x start position: hq_k5pos_kernel (shared-memory slices); the 5-mer totals are the row sums of
@@ -624,10 +630,10 @@ cudaError_t hq_launch_qc_simple(const hq_kargs &a, cudaStream_t st, uint64_t *la
 cudaError_t hq_launch_kmers_cg(const hq_kargs &a0, uint32_t max_len_in_batch, cudaStream_t st, uint64_t *launches) {
   if (a0.n_reads == 0) return cudaSuccess;
   const bool cg = (a0.work & HPGQ_WORK_CHAOS) != 0 && a0.cg_k > 0;
-  // with the packed chaos-game table a sub-launch must stay below 2^26 words (see cg_add)
+  // with the packed chaos-game table a sub-launch must stay below 2^27 words (see cg_add)
   uint32_t chunk = a0.n_reads;
   if (cg && a0.cg_pack) {
-    const uint64_t per = ((1ull << 26) - 1ull) / (max_len_in_batch ? max_len_in_batch : 1u);
+    const uint64_t per = (HQ_PK_WORDS - 1ull) / (max_len_in_batch ? max_len_in_batch : 1u);
     if (per == 0) return cudaErrorInvalidValue;
     if (per < chunk) chunk = (uint32_t)per;
   }

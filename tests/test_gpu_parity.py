@@ -577,6 +577,9 @@ def test_kmers_and_chaos_game_single_reduction_path(q, ob, k2, ck, monkeypatch):
     seq, qual, idx = rand_batch(rng, 20000, 0, 180, p_n=0.02)
     qual = rng.integers(33, 74, size=len(qual)).astype(np.uint8)
     qual[rng.integers(0, len(qual), 500)] = 20  # below the base quality: the word's sum can wrap
+    # stretches of very high quality bytes: window sums of 1024 and more do not fit the packed field either
+    for start in rng.integers(0, len(qual) - 40, 60):
+        qual[start:start + 40] = 200
     seq = seq.copy()
     o = int(idx[100])
     seq[o:o + 60] = ord("T")
