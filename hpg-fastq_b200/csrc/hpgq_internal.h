@@ -43,6 +43,7 @@ struct hq_kargs {
   uint32_t n_tiles;
   uint32_t n_stages;    // depth of the shared-memory ring
   uint32_t uni_len;     // uniform-length kernels: the length every read of the batch has
+  uint32_t kc_bytes;    // k-mer / chaos kernel: 1 = byte loop for every read (HPGQ_KC_BYTES, A/B and tests)
 };
 
 // launchers (return cudaGetLastError()); `launches` is incremented per kernel launched

@@ -200,6 +200,78 @@ __device__ __forceinline__ int base2(uint32_t c) {
   return c == 'A' ? 0 : c == 'C' ? 1 : c == 'G' ? 2 : c == 'T' ? 3 : -1;
 }
 
+// Word-wise form of the rolling loop below for the common case: k-mers and chaos game together (one packed reduction
+// per base), a read of A, C, G, T, N only.  Four bases per 32-bit load and PRMT lookup (2-bit codes, validity flags);
+// the quality sum of the last cg_k bases is a difference of running sums, the older one taken from a 16-entry ring of
+// the lane in shared memory; the two axis-run counters are shift registers of the x and y bits.  Same look-back, same
+// events and counters as the byte loop (which spends ~145 warp instructions per base step and held the kernel at 60 %
+// of the L2 reduction rate, profiles/launches_c4_r2.md).
+__device__ __forceinline__ void kc_fast_chunk(const hq_kargs &a, uint32_t r, uint32_t o, uint32_t cb, uint32_t ce, int k2,
+                                              int ck, uint32_t k2mask, int32_t (*ring)[256], uint32_t &words_out,
+                                              uint32_t &longruns_out) {
+  const uint32_t jb = cb > HQ_LOOKBACK ? cb - HQ_LOOKBACK : 0u, span = ce - jb, tid = threadIdx.x;
+  const uint32_t qoff = (uint32_t)(a.cg_base_quality * ck);
+  const uint32_t *sw = reinterpret_cast<const uint32_t *>(a.seq), *qw = reinterpret_cast<const uint32_t *>(a.qual);
+  unsigned long long *C = a.ctr;
+  uint32_t code = 0, valid = 0, X = 0, Y = 0, words = 0, longruns = 0;
+  int32_t P = 0;
+  const uint32_t w1 = (o + ce - 1u) >> 2;
+  for (uint32_t w = (o + jb) >> 2; w <= w1; ++w) {
+    const uint32_t s4 = __ldg(sw + w), q4 = __ldg(qw + w);
+    const uint32_t sel = hq_selector(hq_prmt(s4, 0u, 0x3120u));
+    const uint32_t b2w = hq_prmt_raw(0x01000000u, 0x02000003u, sel);       // A 0, C 1, G 2, T 3
+    const uint32_t x = s4 ^ hq_prmt_raw(0x43FF41FFu, 0x47FFFF54u, sel);    // zero byte <=> one of A C G T
+    const uint32_t zf = ~(((x & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | x) & 0x80808080u;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const uint32_t j = 4u * w + (uint32_t)i - o;  // position in the read (wraps for the bytes in front of it)
+      if (j - jb >= span) continue;                 // outside [jb, ce)
+      // signed byte i of the quality word (the reference adds `char`s)
+      const int32_t qb = (int32_t)hq_prmt_raw(q4, 0u, (uint32_t)(i | ((8 | i) << 4) | ((8 | i) << 8) | ((8 | i) << 12)));
+      P += qb;
+      const int32_t pold = j >= jb + (uint32_t)ck ? ring[(j - (uint32_t)ck) & 15u][tid] : 0;
+      ring[j & 15u][tid] = P;
+      if ((zf >> (8 * i + 7)) & 1u) {
+        const uint32_t b = (b2w >> (8 * i)) & 3u;
+        code = (code << 2) | b;
+        valid++;
+        X = (X << 1) | (~(b ^ (b >> 1)) & 1u);  // A or T
+        Y = (Y << 1) | (b >> 1);                // G or T
+        if (j >= cb) {
+          const uint32_t qval = (uint32_t)(P - pold) - qoff;
+          const bool kev = valid >= (uint32_t)k2, cev = valid >= (uint32_t)ck;
+          if (kev && cev && qval < HQ_PK_QMAX) {
+            atomicAdd(&a.kc_pack[code & k2mask], (1ull << HQ_PK_SHIFT) | (unsigned long long)qval);
+            words++;
+          } else {
+            if (kev) atomicAdd(&C[a.o_k2 + (code & k2mask)], 1ull);
+            if (cev) {  // the cell from the last cg_k bases: newest base in the top bit
+              uint32_t ix = 0, iy = 0;
+              for (int t = 0; t < ck; ++t) {
+                const uint32_t bb = (code >> (2 * t)) & 3u;
+                ix |= (~(bb ^ (bb >> 1)) & 1u) << (ck - 1 - t);
+                iy |= (bb >> 1) << (ck - 1 - t);
+              }
+              cg_add(a, ((uint64_t)ix << ck) + iy, qval);
+              words++;
+            }
+          }
+          // an axis run that reaches 21 bases (counted from the look-back's start, as the byte loop does)
+          if ((X & 0x3FFFFFu) == 0x1FFFFFu || (Y & 0x3FFFFFu) == 0x1FFFFFu) {
+            longruns++;
+            if (a.cgflag) a.cgflag[r] = 1;
+          }
+        }
+      } else {
+        valid = 0;
+        code = 0;
+      }
+    }
+  }
+  words_out += words;
+  longruns_out += longruns;
+}
+
 // G lanes share one read (G = 4 for short reads: the chunk of a lane is then much longer than the look-back that
 // warms its rolling state up; G = 32 for long reads).
 template <int G>
@@ -216,6 +288,7 @@ __global__ void __launch_bounds__(256) hq_kmers_cg_kernel(hq_kargs a) {
   unsigned long long *C = a.ctr;
   unsigned long long words = 0, longruns = 0;
   const bool merged = a.kc_pack != nullptr && do_k && do_cg && k2 >= ck;
+  __shared__ int32_t kc_ring[16][256];  // kc_fast_chunk: running quality sums of the lane's last 16 bases
 
   for (uint32_t r0 = warp * NG; r0 < a.n_reads; r0 += nwarps * NG) {  // warp-uniform trip count (ballots below)
     const uint32_t r = r0 + giw;
@@ -246,7 +319,14 @@ __global__ void __launch_bounds__(256) hq_kmers_cg_kernel(hq_kargs a) {
 
     const uint32_t chunk = (L + (uint32_t)G - 1u) / (uint32_t)G;
     const uint32_t cb = lig * chunk, ce = min(L, cb + chunk);
-    if (cb < ce) {
+    // HPGQ_KC_BYTES (hq_kargs.kc_bytes): developer A/B and test switch, keeps the byte loop for every read
+    const bool fast = merged && kmers_here && !other && k2 > 0 && ck <= 15 && !a.kc_bytes;
+    if (cb < ce && fast) {
+      uint32_t w32 = 0, l32 = 0;
+      kc_fast_chunk(a, r, o, cb, ce, k2, ck, k2mask, kc_ring, w32, l32);
+      words += w32;
+      longruns += l32;
+    } else if (cb < ce) {
       const uint32_t jb = cb > HQ_LOOKBACK ? cb - HQ_LOOKBACK : 0u;
       uint32_t code = 0, valid = 0; // k-mer rolling state
       uint32_t ix = 0, iy = 0, cnt = 0, accq = 0, run_x = 0, run_y = 0;
