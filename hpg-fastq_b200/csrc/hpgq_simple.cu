@@ -298,14 +298,28 @@ __global__ void __launch_bounds__(256) hq_kmers_cg_kernel(hq_kargs a) {
     const bool kmers_here = do_k && live && (!use_mask || a.mask[r]) && L <= a.Lcap;
     // does the read hold bytes other than A,C,G,T,N?  (changes the chaos-game window arithmetic)
     bool other = false, single_x = true, single_y = true;
-    for (uint32_t j = lig; j < L; j += G) {
-      const uint32_t c = s[j];
-      const int b = base2(c);
-      if (b < 0 && c != 'N') other = true;
-      if (b >= 0) {
-        if (!(b == 0 || b == 3)) single_x = false;
-        if (!(b == 2 || b == 3)) single_y = false;
+    if (L) {
+      // word-wise: the lanes of the group take the aligned words of the read in turn; per word one PRMT lookup gives
+      // "is A/C/G/T" (expected-byte compare) and the two flags that break an axis (C or G: not x; A or C: not y)
+      const uint32_t *sw = reinterpret_cast<const uint32_t *>(a.seq);
+      const uint32_t wl = (o + L - 1u) >> 2;
+      uint32_t f_other = 0u, f_axis = 0u;
+      for (uint32_t w = (o >> 2) + lig; w <= wl; w += G) {
+        const uint32_t s4 = __ldg(sw + w);
+        // bytes of the word inside [o, o + L)
+        const uint32_t m = hq_tail_mask(4u * w, o + L) & ~hq_tail_mask(4u * w, o);
+        const uint32_t sel = hq_selector(hq_prmt(s4, 0u, 0x3120u));
+        const uint32_t x = s4 ^ hq_prmt_raw(0x43FF41FFu, 0x47FFFF54u, sel);   // zero byte <=> one of A C G T
+        const uint32_t acgt = ~(((x & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | x) & 0x80808080u;
+        const uint32_t xn = s4 ^ 0x4E4E4E4Eu;
+        const uint32_t isn = ~(((xn & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | xn) & 0x80808080u;
+        f_other |= ~(acgt | isn) & 0x80808080u & m;
+        // A (index 1): 0x02, C (3): 0x03, T (4): 0x00, G (7): 0x01
+        f_axis |= hq_prmt_raw(0x03000200u, 0x01000000u, sel) & (acgt >> 7) * 3u & m;
       }
+      other = f_other != 0u;
+      single_x = (f_axis & 0x01010101u) == 0u;
+      single_y = (f_axis & 0x02020202u) == 0u;
     }
     other = (__ballot_sync(0xFFFFFFFFu, other) & gmask) != 0u;
     single_x = (__ballot_sync(0xFFFFFFFFu, single_x) & gmask) == gmask;
