@@ -200,76 +200,100 @@ __device__ __forceinline__ int base2(uint32_t c) {
   return c == 'A' ? 0 : c == 'C' ? 1 : c == 'G' ? 2 : c == 'T' ? 3 : -1;
 }
 
+// MODE 0: every base checked against [jb, ce) and cb (the words at the chunk's ends and the one that holds cb);
+// MODE 1: whole word inside the look-back (state only); MODE 2: whole word inside [cb, ce).
+struct kc_state {
+  uint32_t code, valid, X, Y, words, longruns;
+  int32_t P;
+};
+
+template <int MODE>
+__device__ __forceinline__ void kc_fast_word(const hq_kargs &a, kc_state &st, uint32_t r, uint32_t w, uint32_t o, uint32_t jb,
+                                             uint32_t cb, uint32_t ce, int k2, int ck, uint32_t k2mask, uint32_t qoff,
+                                             int32_t (*ring)[256]) {
+  const uint32_t tid = threadIdx.x;
+  const uint32_t s4 = __ldg(reinterpret_cast<const uint32_t *>(a.seq) + w);
+  const uint32_t q4 = __ldg(reinterpret_cast<const uint32_t *>(a.qual) + w);
+  const uint32_t sel = hq_selector(hq_prmt(s4, 0u, 0x3120u));
+  const uint32_t b2w = hq_prmt_raw(0x01000000u, 0x02000003u, sel);       // A 0, C 1, G 2, T 3
+  const uint32_t x = s4 ^ hq_prmt_raw(0x43FF41FFu, 0x47FFFF54u, sel);    // zero byte <=> one of A C G T
+  const uint32_t zf = ~(((x & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | x) & 0x80808080u;
+  unsigned long long *C = a.ctr;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const uint32_t j = 4u * w + (uint32_t)i - o;  // position in the read (wraps for the bytes in front of it)
+    if (MODE == 0 && j - jb >= ce - jb) continue; // outside [jb, ce)
+    // signed byte i of the quality word (the reference adds `char`s)
+    const int32_t qb = (int32_t)hq_prmt_raw(q4, 0u, (uint32_t)(i | ((8 | i) << 4) | ((8 | i) << 8) | ((8 | i) << 12)));
+    st.P += qb;
+    int32_t pold = 0;
+    if (MODE != 1) {
+      pold = ring[(j - (uint32_t)ck) & 15u][tid];
+      if (j < jb + (uint32_t)ck) pold = 0;
+    }
+    ring[j & 15u][tid] = st.P;
+    const bool ok = ((zf >> (8 * i + 7)) & 1u) != 0u;
+    const uint32_t b = (b2w >> (8 * i)) & 3u;
+    // state by selection, not by branch
+    st.code = ok ? ((st.code << 2) | b) : 0u;
+    st.valid = ok ? st.valid + 1u : 0u;
+    st.X = ok ? ((st.X << 1) | (~(b ^ (b >> 1)) & 1u)) : st.X;  // A or T
+    st.Y = ok ? ((st.Y << 1) | (b >> 1)) : st.Y;                // G or T
+    if (MODE == 1) continue;
+    const bool emit = ok && (MODE == 2 || j >= cb);
+    const uint32_t qval = (uint32_t)(st.P - pold) - qoff;
+    const bool kev = st.valid >= (uint32_t)k2, cev = st.valid >= (uint32_t)ck;
+    if (emit && kev && cev && qval < HQ_PK_QMAX) {
+      atomicAdd(&a.kc_pack[st.code & k2mask], (1ull << HQ_PK_SHIFT) | (unsigned long long)qval);
+      st.words++;
+    } else if (emit && (kev || cev)) {
+      if (kev) atomicAdd(&C[a.o_k2 + (st.code & k2mask)], 1ull);
+      if (cev) {  // the cell from the last cg_k bases: newest base in the top bit
+        uint32_t ix = 0, iy = 0;
+        for (int t = 0; t < ck; ++t) {
+          const uint32_t bb = (st.code >> (2 * t)) & 3u;
+          ix |= (~(bb ^ (bb >> 1)) & 1u) << (ck - 1 - t);
+          iy |= (bb >> 1) << (ck - 1 - t);
+        }
+        cg_add(a, ((uint64_t)ix << ck) + iy, qval);
+        st.words++;
+      }
+    }
+    // an axis run that reaches 21 bases
+    if (emit && ((st.X & 0x3FFFFFu) == 0x1FFFFFu || (st.Y & 0x3FFFFFu) == 0x1FFFFFu)) {
+      st.longruns++;
+      if (a.cgflag) a.cgflag[r] = 1;
+    }
+  }
+}
+
 // Word-wise form of the rolling loop below for the common case: k-mers and chaos game together (one packed reduction
 // per base), a read of A, C, G, T, N only.  Four bases per 32-bit load and PRMT lookup (2-bit codes, validity flags);
 // the quality sum of the last cg_k bases is a difference of running sums, the older one taken from a 16-entry ring of
-// the lane in shared memory; the two axis-run counters are shift registers of the x and y bits.  Same look-back, same
-// events and counters as the byte loop (which spends ~145 warp instructions per base step and held the kernel at 60 %
-// of the L2 reduction rate, profiles/launches_c4_r2.md).
+// the lane in shared memory; the two axis-run counters are shift registers of the x and y bits; the rolling state is
+// updated by selection.  Same look-back, same events as the byte loop (which spends ~145 warp instructions per base
+// step and held the kernel at 60 % of the L2 reduction rate, profiles/launches_c4_r2.md).
 __device__ __forceinline__ void kc_fast_chunk(const hq_kargs &a, uint32_t r, uint32_t o, uint32_t cb, uint32_t ce, int k2,
                                               int ck, uint32_t k2mask, int32_t (*ring)[256], uint32_t &words_out,
                                               uint32_t &longruns_out) {
-  const uint32_t jb = cb > HQ_LOOKBACK ? cb - HQ_LOOKBACK : 0u, span = ce - jb, tid = threadIdx.x;
+  const uint32_t jb = cb > HQ_LOOKBACK ? cb - HQ_LOOKBACK : 0u;
   const uint32_t qoff = (uint32_t)(a.cg_base_quality * ck);
-  const uint32_t *sw = reinterpret_cast<const uint32_t *>(a.seq), *qw = reinterpret_cast<const uint32_t *>(a.qual);
-  unsigned long long *C = a.ctr;
-  uint32_t code = 0, valid = 0, X = 0, Y = 0, words = 0, longruns = 0;
-  int32_t P = 0;
-  const uint32_t w1 = (o + ce - 1u) >> 2;
-  for (uint32_t w = (o + jb) >> 2; w <= w1; ++w) {
-    const uint32_t s4 = __ldg(sw + w), q4 = __ldg(qw + w);
-    const uint32_t sel = hq_selector(hq_prmt(s4, 0u, 0x3120u));
-    const uint32_t b2w = hq_prmt_raw(0x01000000u, 0x02000003u, sel);       // A 0, C 1, G 2, T 3
-    const uint32_t x = s4 ^ hq_prmt_raw(0x43FF41FFu, 0x47FFFF54u, sel);    // zero byte <=> one of A C G T
-    const uint32_t zf = ~(((x & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | x) & 0x80808080u;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const uint32_t j = 4u * w + (uint32_t)i - o;  // position in the read (wraps for the bytes in front of it)
-      if (j - jb >= span) continue;                 // outside [jb, ce)
-      // signed byte i of the quality word (the reference adds `char`s)
-      const int32_t qb = (int32_t)hq_prmt_raw(q4, 0u, (uint32_t)(i | ((8 | i) << 4) | ((8 | i) << 8) | ((8 | i) << 12)));
-      P += qb;
-      const int32_t pold = j >= jb + (uint32_t)ck ? ring[(j - (uint32_t)ck) & 15u][tid] : 0;
-      ring[j & 15u][tid] = P;
-      if ((zf >> (8 * i + 7)) & 1u) {
-        const uint32_t b = (b2w >> (8 * i)) & 3u;
-        code = (code << 2) | b;
-        valid++;
-        X = (X << 1) | (~(b ^ (b >> 1)) & 1u);  // A or T
-        Y = (Y << 1) | (b >> 1);                // G or T
-        if (j >= cb) {
-          const uint32_t qval = (uint32_t)(P - pold) - qoff;
-          const bool kev = valid >= (uint32_t)k2, cev = valid >= (uint32_t)ck;
-          if (kev && cev && qval < HQ_PK_QMAX) {
-            atomicAdd(&a.kc_pack[code & k2mask], (1ull << HQ_PK_SHIFT) | (unsigned long long)qval);
-            words++;
-          } else {
-            if (kev) atomicAdd(&C[a.o_k2 + (code & k2mask)], 1ull);
-            if (cev) {  // the cell from the last cg_k bases: newest base in the top bit
-              uint32_t ix = 0, iy = 0;
-              for (int t = 0; t < ck; ++t) {
-                const uint32_t bb = (code >> (2 * t)) & 3u;
-                ix |= (~(bb ^ (bb >> 1)) & 1u) << (ck - 1 - t);
-                iy |= (bb >> 1) << (ck - 1 - t);
-              }
-              cg_add(a, ((uint64_t)ix << ck) + iy, qval);
-              words++;
-            }
-          }
-          // an axis run that reaches 21 bases (counted from the look-back's start, as the byte loop does)
-          if ((X & 0x3FFFFFu) == 0x1FFFFFu || (Y & 0x3FFFFFu) == 0x1FFFFFu) {
-            longruns++;
-            if (a.cgflag) a.cgflag[r] = 1;
-          }
-        }
-      } else {
-        valid = 0;
-        code = 0;
-      }
-    }
-  }
-  words_out += words;
-  longruns_out += longruns;
+  kc_state st = {0u, 0u, 0u, 0u, 0u, 0u, 0};
+  // words: [w0, wa) generic (the partial first word), [wa, wc) look-back only, [wc, wd) generic (the word holding cb),
+  // [wd, we) emit, [we, w1] generic (the partial last word)
+  const uint32_t w0 = (o + jb) >> 2, w1 = (o + ce - 1u) >> 2;
+  const uint32_t wa = min(w1 + 1u, (o + jb + 3u) >> 2);               // first word that lies wholly at or behind jb
+  const uint32_t wc = max(wa, min(w1 + 1u, (o + cb) >> 2));           // word that holds cb
+  const uint32_t wd = min(w1 + 1u, max(wc, (o + cb + 3u) >> 2));      // first word wholly at or behind cb
+  const uint32_t we = max(wd, (o + ce) >> 2);                         // first word not wholly in front of ce
+  uint32_t w = w0;
+  for (; w < wa; ++w) kc_fast_word<0>(a, st, r, w, o, jb, cb, ce, k2, ck, k2mask, qoff, ring);
+  for (; w < wc; ++w) kc_fast_word<1>(a, st, r, w, o, jb, cb, ce, k2, ck, k2mask, qoff, ring);
+  for (; w < wd; ++w) kc_fast_word<0>(a, st, r, w, o, jb, cb, ce, k2, ck, k2mask, qoff, ring);
+  for (; w < we; ++w) kc_fast_word<2>(a, st, r, w, o, jb, cb, ce, k2, ck, k2mask, qoff, ring);
+  for (; w <= w1; ++w) kc_fast_word<0>(a, st, r, w, o, jb, cb, ce, k2, ck, k2mask, qoff, ring);
+  words_out += st.words;
+  longruns_out += st.longruns;
 }
 
 // G lanes share one read (G = 4 for short reads: the chunk of a lane is then much longer than the look-back that
