@@ -259,20 +259,21 @@ __device__ __forceinline__ void fz_cp16(void *dst_smem, const void *src) {
 __device__ __forceinline__ void ct_emit(const ct_hdr &h, const uint8_t *rmap, uint32_t mo_f, const uint8_t *sseq,
                                         const uint8_t *squal, uint32_t nt, uint8_t *const oseq[2], uint8_t *const oqual[2]) {
   const uint32_t tid = threadIdx.x;
-#pragma unroll 1
-  for (int stream = 0; stream < 2; ++stream) {
-    const uint32_t *key = h.key[stream];
-    // selected here, in registers: indexing the two-entry pointer arrays with the loop variable put them in local
-    // memory and a dependent LDL in front of every store (18 % of the stall samples of the gather kernel)
-    uint8_t *const os = stream ? oseq[1] : oseq[0], *const oq = stream ? oqual[1] : oqual[0];
-    const uint32_t D0 = key[0], D1 = key[nt];
-    if (D1 == D0) continue;
-    // a warp owns a contiguous run of the span's chunks, so the read index only moves forward between its rounds
-    const uint32_t c_lo = D0 >> 4, c_hi = (D1 + 15u) >> 4;
-    const uint32_t per = (c_hi - c_lo + 7u) >> 3;
-    const uint32_t w_lo = c_lo + (tid >> 5) * per, w_hi = min(c_hi, w_lo + per);
-    const uint8_t *mp = rmap + (stream ? mo_f : 0u) - c_lo;
-    for (uint32_t c = w_lo + (tid & 31u); c < w_hi; c += 32u) {
+  // ONE loop over the chunks of both spans (passed span first): the failed span of a tile is a few chunks, and a loop of
+  // its own cost every warp a round with one or two active lanes (19 of 32 lanes were active on average)
+  const uint32_t D00 = h.key[0][0], D01 = h.key[0][nt], D10 = h.key[1][0], D11 = h.key[1][nt];
+  const uint32_t c0 = D00 >> 4, n0 = D01 > D00 ? ((D01 + 15u) >> 4) - c0 : 0u;
+  const uint32_t c1 = D10 >> 4, n1 = D11 > D10 ? ((D11 + 15u) >> 4) - c1 : 0u;
+  {
+    for (uint32_t v = tid; v < n0 + n1; v += blockDim.x) {
+      const bool s1 = v >= n0;
+      const uint32_t *key = &h.key[0][0] + (s1 ? CT_RPT + 1u : 0u);  // offsets, not pointer selects: stays an LDS
+      const uint32_t D0 = s1 ? D10 : D00, D1 = s1 ? D11 : D01;
+      const uint32_t c = s1 ? c1 + (v - n0) : c0 + v, c_hi = (D1 + 15u) >> 4;
+      const uint8_t *mp = rmap + (int32_t)(s1 ? mo_f - c1 : 0u - c0);
+      // pointers selected into registers (as two-entry arrays indexed by a loop variable they lived in local memory:
+      // a dependent LDL in front of every store, 18 % of the stall samples of the gather kernel)
+      uint8_t *const os = s1 ? oseq[1] : oseq[0], *const oq = s1 ? oqual[1] : oqual[0];
       const uint32_t dc = c << 4, d0 = max(dc, D0), d1 = min(dc + 16u, D1);
       const uint32_t r = mp[c];
       const uint32_t kend = key[r + 1];
