@@ -416,10 +416,10 @@ __global__ void __launch_bounds__(256) hq_compact_copy_tile(hq_kargs a, hq_compa
 // mask bytes, trim records and its source span -- is sent to shared memory with cp.async while tile t is being built,
 // and the two offsets that size the copies of tile t + 2 are loaded into registers one iteration ahead.
 struct ct_raw_t {
-  uint4 scan[CT_RPT / 2 + 2];
-  uint32_t idx[CT_RPT / 2 + 4];
-  hpgq_trim_t trim[CT_RPT / 2];
-  uint32_t mask[CT_RPT / 8 + 2];  // the aligned words that hold the tile's mask bytes
+  uint4 scan[CT_RPT + 2];
+  uint32_t idx[CT_RPT + 4];
+  hpgq_trim_t trim[CT_RPT];
+  uint32_t mask[CT_RPT / 4 + 2];  // the aligned words that hold the tile's mask bytes
 };
 
 __device__ __forceinline__ void ct_cp(void *dst_smem, const void *src, int bytes) {
@@ -1193,14 +1193,26 @@ cudaError_t hq_launch_compact(const hq_kargs &a, const hq_compact_bufs &b, uint3
       uint32_t tiles = (a.n_reads + rpt - 1u) / rpt;
       if (tiles > 148u * 8u) tiles = 148u * 8u;
       // two buffers of half-size tiles when at least two such tiles per CTA exist (HPGQ_CT_SINGLE: developer A/B)
-      const uint32_t rpt2 = rpt >= 32u ? rpt / 2u : 0u;
+      uint32_t rpt2 = rpt >= 32u ? rpt / 2u : 0u;
+      static const uint32_t knob_rpt = getenv("HPGQ_CT_RPT2") ? (uint32_t)atoi(getenv("HPGQ_CT_RPT2")) : 0u;    // developer knobs
+      static const uint32_t knob_ctas = getenv("HPGQ_CT_CTAS") ? (uint32_t)atoi(getenv("HPGQ_CT_CTAS")) : 0u;
+      if (rpt2 && knob_rpt >= 8u && knob_rpt <= CT_RPT && knob_rpt * max_len <= CT_SPAN) rpt2 = knob_rpt;
       if (rpt2 && !getenv("HPGQ_CT_SINGLE")) {
         const uint32_t cap2 = ((rpt2 * max_len + 15u) & ~15u) + 64u;
         const uint32_t smem2 = (((uint32_t)sizeof(ct_hdr) + 15u) & ~15u) +
                                2u * ((((uint32_t)sizeof(ct_raw_t) + 15u) & ~15u) + ct_rmap_bytes(cap2) + 2u * cap2);
         uint32_t tiles2 = (a.n_reads + rpt2 - 1u) / rpt2;
-        if (tiles2 > 148u * 5u) tiles2 = 148u * 5u;
-        if (smem2 <= 48u * 1024u) {
+        if (smem2 <= 100u * 1024u) {
+          if (smem2 > 48u * 1024u) {
+            cudaError_t e = cudaFuncSetAttribute(hq_compact_copy_tile2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
+            if (e != cudaSuccess) return e;
+          }
+          // a grid-stride loop over tiles: exactly as many CTAs as are resident at once (a fifth CTA per SM that has to
+          // wait for a slot runs as a second wave: 1.08 against 0.99 ms per C3 batch, profiles/sweep_c3_r2f.log)
+          int occ = 0;
+          if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, hq_compact_copy_tile2, 256, smem2) != cudaSuccess || occ < 1) occ = 4;
+          const uint32_t ctas = knob_ctas ? knob_ctas : (uint32_t)occ;
+          if (tiles2 > 148u * ctas) tiles2 = 148u * ctas;
           hq_compact_copy_tile2<<<tiles2, 256, smem2, st>>>(a, b, rpt2, cap2);
           ++*launches;
           return cudaGetLastError();
