@@ -763,7 +763,7 @@ template <int MODE>
 cudaError_t launch_pos_mode(const hq_kargs &a, uint32_t max_len_in_batch, int sm_count, cudaStream_t st, uint64_t *launches) {
   const uint32_t cover = max_len_in_batch < a.Lcap ? max_len_in_batch : a.Lcap;
   const uint32_t tiles = (cover + POS_TILE - 1u) / POS_TILE;
-  // 2 CTAs are resident per SM (67 KB ring each, <= 128 registers): four waves, the tiles near the longest reads
+  // 2 CTAs are resident per SM (100 KB ring each: 3 stages x 8 reads x 2 arrays x 2 080 bytes, <= 128 registers): four waves, the tiles near the longest reads
   // see few reads and finish early
   uint32_t slabs = ((uint32_t)sm_count * 8u) / tiles;
   // a thread widens its packed lanes every 248 reads and keeps u32 sums: any slab size is safe below 2^24 reads
