@@ -12,7 +12,7 @@ struct geom_entry {
   int K, G;
 };
 // capacity 4*K*G bases; keep in sync with the HQT_INSTANTIATE lists in hpgq_tiled_g*.cu
-const geom_entry kGeoms[] = {{2, 4}, {3, 4}, {4, 4}, {5, 4}, {5, 5}, {3, 8}, {4, 8}, {5, 8},
+const geom_entry kGeoms[] = {{2, 4}, {3, 4}, {4, 4}, {5, 4}, {7, 4}, {5, 5}, {3, 8}, {4, 8}, {5, 8},
                              {3, 16}, {4, 16}, {5, 16}, {3, 32}, {4, 32}, {5, 32}};
 
 struct hq_geom {
@@ -43,6 +43,7 @@ bool pick_geom(uint32_t max_len, bool uniform, uint32_t n_reads, int sm_count, s
   int bK = 0, bG = 0;
   for (const geom_entry &ge : kGeoms) {
     if ((uint32_t)(ge.K * ge.G) < words) continue;
+    if (ge.K > 5 && !uniform) continue;  // 7 words per lane: only the aligned-word loop keeps them in registers
     if (4 * ge.K * ge.G <= 256 && max_len > 255u) continue;  // packed group sum holds 8-bit base counts
     const uint32_t NG = 32u / (uint32_t)ge.G;
     if (uniform && (((NG * max_len) & 3u) != 0u || max_len < 4u * (uint32_t)((ge.K - 1) * ge.G))) continue;
@@ -127,7 +128,7 @@ cudaError_t hq_launch_qc_tiled(hq_kargs a, uint32_t max_len_in_batch, bool unifo
   cudaError_t e = cudaErrorInvalidValue;
 #define HQ_CASE(KK, GG) \
   if (gm.K == KK && gm.G == GG) e = launch_kg<KK, GG>(a, full, uni, grid, gm.smem_bytes, st);
-  HQ_CASE(2, 4) HQ_CASE(3, 4) HQ_CASE(4, 4) HQ_CASE(5, 4) HQ_CASE(5, 5)
+  HQ_CASE(2, 4) HQ_CASE(3, 4) HQ_CASE(4, 4) HQ_CASE(5, 4) HQ_CASE(7, 4) HQ_CASE(5, 5)
   HQ_CASE(3, 8) HQ_CASE(4, 8) HQ_CASE(5, 8)
   HQ_CASE(3, 16) HQ_CASE(4, 16) HQ_CASE(5, 16)
   HQ_CASE(3, 32) HQ_CASE(4, 32) HQ_CASE(5, 32)

@@ -5,4 +5,5 @@ HQT_INSTANTIATE(2, 4)
 HQT_INSTANTIATE(3, 4)
 HQT_INSTANTIATE(4, 4)
 HQT_INSTANTIATE(5, 4)
+HQT_INSTANTIATE(7, 4)
 }  // namespace hqt

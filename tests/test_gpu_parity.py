@@ -417,7 +417,7 @@ def test_bench_shaped_launch_matches_oracle(q, ob, no_uni):
 
 
 @pytest.mark.parametrize("no_uni", [None, 1])
-@pytest.mark.parametrize("L,n", [(76, 70000), (150, 36000), (300, 18000), (600, 9500), (36, 140000)])
+@pytest.mark.parametrize("L,n", [(76, 70000), (150, 36000), (300, 18000), (600, 9500), (36, 140000), (100, 60000)])
 def test_in_loop_flush_every_geometry(q, ob, L, n, no_uni):
     """Two CTAs (HPGQ_GRID_CAP): each consumer warp passes iteration 255 of every ladder cadence
     (G = 4, 8, 16, 32: MERGED and !MERGED), uniform reads and a ragged variant."""
@@ -430,7 +430,7 @@ def test_in_loop_flush_every_geometry(q, ob, L, n, no_uni):
             _device_check(q, ob, par, seq, qual, idx, 640)
 
 
-@pytest.mark.parametrize("L", [7, 36, 75, 100, 101, 149, 150, 151, 250, 251, 253, 300, 301, 302, 600, 637, 640])
+@pytest.mark.parametrize("L", [7, 36, 75, 96, 97, 100, 101, 106, 111, 112, 113, 149, 150, 151, 250, 251, 253, 300, 301, 302, 600, 637, 640])
 def test_uniform_kernel_lengths_and_phases(q, ob, L):
     """Uniform-length kernel over the geometries' length range, odd lengths (where the group count does not keep the
     byte phase the kernel must not be chosen) and every start phase idx[0] mod 4 / mod 16."""
