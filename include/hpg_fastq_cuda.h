@@ -255,7 +255,9 @@ int hpgq_batch_wait_text(hpgq_ctx_t *ctx, int slot, hpgq_batch_result_t *res, co
  * fd_passed and the failed reads' records to fd_failed, each at the descriptor's file position, while the rest of
  * the text is still on its way back through the ctx's pinned output ring -- no chunk-sized host buffer.  A regular
  * file opened read-write is extended and filled through a mapping by the pool threads; any other descriptor gets
- * write().  A descriptor may be -1 when the batch has no records for it (edit without filter: no failed reads). */
+ * write().  (The mapping is used only while the file system reports room for the bytes plus a margin: a store into a
+ * mapped page that cannot be backed would raise SIGBUS where write() returns ENOSPC.)  A descriptor may be -1 when the
+ * batch has no records for it (edit without filter: no failed reads). */
 int hpgq_batch_wait_text_fd(hpgq_ctx_t *ctx, int slot, hpgq_batch_result_t *res, int fd_passed, int fd_failed,
                             uint64_t *passed_bytes, uint64_t *failed_bytes);
 /* Optional: allocates the text path's buffers (pinned rings, per-slot device chunk + parser scratch, and with
