@@ -179,20 +179,25 @@ HQ_HDI hq_dec2_t hq_decode2_fma(uint32_t swm, uint32_t p20) {
 
 // exact per-byte twin for words holding foreign bytes; only bytes selected by m are looked at.
 // other = 0x01 per in-read byte that is none of A,C,G,T,N
+// 0x01 in every byte of x that equals the byte of pat (pat = one byte value replicated)
+HQ_HDI uint32_t hq_eq_bytes(uint32_t x, uint32_t pat) {
+  const uint32_t d = x ^ pat;
+  return (~(((d & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | d) & 0x80808080u) >> 7;
+}
+
+// Exact classification of the bytes selected by m (0xFF per byte inside the read): C/G and A/T flags as in
+// hq_decode2, *other = 0x01 per byte that is none of A, C, G, T, N.  Branch-free: every lane of the warp runs
+// the same instructions whatever its bytes are.
 HQ_HDI hq_dec2_t hq_decode2_exact(uint32_t sw, uint32_t m, uint32_t *other) {
   hq_dec2_t d;
-  d.cg = d.at = d.bad = 0u;
-  uint32_t oth = 0u;
-  for (int i = 0; i < 4; ++i) {
-    if (!((m >> (8 * i)) & 1u)) continue;
-    const uint32_t c = (sw >> (8 * i)) & 0xFFu;
-    if (c == 'C') d.cg |= 0x01u << (8 * i);
-    else if (c == 'G') d.cg |= 0x10u << (8 * i);
-    else if (c == 'A') d.at |= 0x01u << (8 * i);
-    else if (c == 'T') d.at |= 0x10u << (8 * i);
-    else if (c != 'N') oth |= 0x01u << (8 * i);
-  }
-  *other = oth;
+  const uint32_t in = m & 0x01010101u;
+  const uint32_t zc = hq_eq_bytes(sw, 0x43434343u), zg = hq_eq_bytes(sw, 0x47474747u);
+  const uint32_t za = hq_eq_bytes(sw, 0x41414141u), zt = hq_eq_bytes(sw, 0x54545454u);
+  const uint32_t zn = hq_eq_bytes(sw, 0x4E4E4E4Eu);
+  d.cg = (zc | (zg << 4)) & (in * 0x11u);
+  d.at = (za | (zt << 4)) & (in * 0x11u);
+  d.bad = 0u;
+  *other = in & ~(zc | zg | za | zt | zn);
   return d;
 }
 

@@ -1,0 +1,136 @@
+#!/usr/bin/env python
+"""Randomised parity stress on the GPU box: random batch shapes and option sets through the C ABI, every counter,
+mask, trim record and compacted array compared with the oracle (test infrastructure, like tests/).  Developer tool:
+    python tools/stress_parity.py [--cases 60] [--seed 1]
+Prints one line per case and exits non-zero at the first difference."""
+from __future__ import annotations
+
+import argparse
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+IGNORE = ("SLOW_READS", "BATCHES", "CG_LONG_RUNS", "CG_FIXED_READS", "CG_MOVED_WORDS", "BAD_BATCH")
+
+
+def rand_batch(rng, n, lmin, lmax, p_n, lower, uniform, hiq):
+    lens = np.full(n, lmax) if uniform else rng.integers(lmin, lmax + 1, size=n)
+    idx = np.zeros(n + 1, dtype=np.uint32)
+    idx[1:] = np.cumsum(lens)
+    tot = int(idx[-1])
+    seq = rng.choice(np.frombuffer(b"ACGTN", dtype=np.uint8), size=tot, p=[(1 - p_n) / 4] * 4 + [p_n]).astype(np.uint8)
+    if lower > 0 and tot:
+        m = rng.random(tot) < lower
+        seq[m] |= 0x20
+    qual = rng.integers(33, 75, size=tot).astype(np.uint8)
+    if tot:
+        # poly-A / poly-T / poly-G stretches (chaos-game axis runs) and stretches of odd quality bytes
+        for _ in range(int(rng.integers(0, 6))):
+            s = int(rng.integers(0, tot))
+            seq[s:s + int(rng.integers(10, 90))] = rng.choice(np.frombuffer(b"ATG", dtype=np.uint8))
+        if hiq:
+            for _ in range(int(rng.integers(1, 5))):
+                s = int(rng.integers(0, tot))
+                qual[s:s + int(rng.integers(1, 40))] = int(rng.choice([20, 126, 200, 255]))
+    return seq, qual, idx
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--cases", type=int, default=60)
+    ap.add_argument("--seed", type=int, default=1)
+    args = ap.parse_args()
+    import __graft_entry__ as g
+    import oracle_binding as ob
+    q = g.load_package().hpgq
+    ob.lib()
+    rng = np.random.default_rng(args.seed)
+    skip = {q.S[k] for k in IGNORE}
+    for case in range(args.cases):
+        kind = rng.choice(["short", "short", "mid", "long", "tiny"])
+        lmin, lmax, n = {"short": (int(rng.integers(1, 60)), int(rng.integers(60, 400)), int(rng.integers(1, 40000))),
+                         "mid": (int(rng.integers(100, 640)), int(rng.integers(641, 1100)), int(rng.integers(1, 4000))),
+                         "long": (int(rng.integers(200, 3000)), int(rng.integers(3000, 12000)), int(rng.integers(1, 600))),
+                         "tiny": (0, int(rng.integers(1, 40)), int(rng.integers(0, 300)))}[kind]
+        uniform = bool(rng.random() < 0.3) and lmax > 0
+        mode = rng.choice(["stats", "stats_filter", "filter_compact", "edit", "kmers", "kmers_chaos", "all_stats"])
+        flt = dict(min_read_length=int(rng.integers(0, max(lmax // 2, 1))), min_read_quality=int(rng.integers(0, 30)),
+                   max_N=int(rng.integers(0, max(lmax // 10, 2))))
+        if rng.random() < 0.3:
+            flt.update(max_read_length=int(rng.integers(lmax // 2 + 1, 2 * lmax + 2)), max_read_quality=int(rng.integers(30, 45)))
+        if rng.random() < 0.25:
+            flt.update(max_out_of_quality=int(rng.integers(0, lmax + 1)), left_length=int(rng.integers(1, 30)),
+                       min_left_quality=int(rng.integers(5, 30)), right_length=int(rng.integers(1, 30)),
+                       min_right_quality=int(rng.integers(5, 30)))
+        edit = dict(left_length=int(rng.integers(0, 40)), min_left_quality=int(rng.integers(10, 38)),
+                    right_length=int(rng.integers(0, 40)), min_right_quality=int(rng.integers(10, 38)))
+        k2, ck = int(rng.integers(2, 12)), int(rng.integers(2, 11))
+        ctxkw, parkw = {}, {}
+        if mode == "stats":
+            work = q.WORK_STATS
+        elif mode == "stats_filter":
+            work, parkw = q.WORK_STATS | q.WORK_FILTER, dict(filter=flt)
+        elif mode == "filter_compact":
+            work, parkw = q.WORK_FILTER | q.WORK_COMPACT, dict(filter=flt)
+        elif mode == "edit":
+            work = q.WORK_EDIT | q.WORK_COMPACT | (q.WORK_FILTER if rng.random() < 0.7 else 0)
+            parkw = dict(edit=edit, filter=flt if work & q.WORK_FILTER else None)
+        elif mode == "kmers":
+            work, parkw, ctxkw = q.WORK_KMERS, dict(k2=k2), dict(kmers=True, k2=k2)
+        elif mode == "kmers_chaos":
+            work, parkw, ctxkw = q.WORK_KMERS | q.WORK_CHAOS, dict(k2=k2, cg_k=ck), dict(kmers=True, k2=k2, cg_k=ck)
+        else:
+            work = q.WORK_STATS | q.WORK_FILTER | q.WORK_KMERS | q.WORK_CHAOS
+            parkw, ctxkw = dict(filter=flt, k2=k2, cg_k=ck), dict(kmers=True, k2=k2, cg_k=ck)
+        if (work & (q.WORK_KMERS | q.WORK_CHAOS)) and kind == "long":
+            n = min(n, 80)
+        seq, qual, idx = rand_batch(rng, n, lmin, lmax, float(rng.choice([0.0, 0.01, 0.05])),
+                                    float(rng.choice([0.0, 0.0, 0.01])), uniform, bool(rng.random() < 0.3))
+        par = q.make_params(int(work), **parkw)
+        Lcap = (max(lmax, 1) + 63) // 64 * 64
+        desc = f"case {case}: {kind} n={n} L={lmin}-{lmax}{' uniform' if uniform else ''} {mode} k2={k2} ck={ck}"
+        with q.Ctx(0, max_reads=max(n, 1), max_bytes=max(int(idx[-1]), 16), max_read_len=Lcap, **ctxkw) as ctx:
+            ctx.set_params(par)
+            ctx.submit(seq, qual, idx, 0)
+            res = ctx.wait(0)
+            got, lay = ctx.counters(), ctx.layout
+        exp, emask, etrim = ob.process_batch(par, lay, seq, qual, idx)
+        bad = [int(b) for b in np.nonzero(got != exp)[0] if int(b) not in skip]
+        ok = not bad and np.array_equal(res["mask"], emask)
+        if ok and (work & q.WORK_EDIT):
+            ok = np.array_equal(res["trim"], etrim)
+        if ok and (work & q.WORK_COMPACT):
+            cp = ob.compact(seq, qual, idx, emask if work & q.WORK_FILTER else None, etrim if work & q.WORK_EDIT else None)
+            ok = all(np.array_equal(res[k], cp[k]) for k in ("out_idx", "out_src", "out_seq", "out_qual"))
+        print(("ok   " if ok else "FAIL ") + desc + (f" first bad words {bad[:6]}" if bad else ""), flush=True)
+        if not ok:
+            names = {v: k for k, v in q.S.items()}
+            for b in bad[:10]:
+                print(f"     word {b} ({names.get(b, 'table')}): got {int(got[b])} exp {int(exp[b])}")
+            print(f"     mask differs at {np.nonzero(res['mask'] != emask)[0][:8]}, max quality byte {int(qual.max()) if len(qual) else 0}, "
+                  f"filter {flt if work & q.WORK_FILTER else None}, edit {edit if work & q.WORK_EDIT else None}")
+            for env in ({"HPGQ_NO_UNI": "1"}, {"HPGQ_NO_POSFUSE": "1"}, {"VARIANT": "1"}):
+                os.environ.update({k: v for k, v in env.items() if k != "VARIANT"})
+                par2 = q.make_params(int(work), kernel_variant=1 if "VARIANT" in env else 0, **parkw)
+                with q.Ctx(0, max_reads=max(n, 1), max_bytes=max(int(idx[-1]), 16), max_read_len=Lcap, **ctxkw) as ctx:
+                    ctx.set_params(par2)
+                    ctx.submit(seq, qual, idx, 0)
+                    r2 = ctx.wait(0)
+                    g2 = ctx.counters()
+                b2 = [int(b) for b in np.nonzero(g2 != exp)[0] if int(b) not in skip]
+                print(f"     with {env}: {len(b2)} bad words, mask equal {np.array_equal(r2['mask'], emask)}")
+                for k in env:
+                    os.environ.pop(k, None)
+            np.savez(os.path.join(ROOT, "gpurun_out", f"stress_fail_{args.seed}_{case}.npz"), seq=seq, qual=qual, idx=idx)
+            return 1
+    print(f"{args.cases} cases ok (seed {args.seed})")
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())
