@@ -1,7 +1,9 @@
 #!/usr/bin/env python
 """Randomised parity stress on the GPU box: random batch shapes and option sets through the C ABI, every counter,
 mask, trim record and compacted array compared with the oracle (test infrastructure, like tests/).  Developer tool:
-    python tools/stress_parity.py [--cases 60] [--seed 1]
+    python tools/stress_parity.py [--cases 60] [--seed 1] [--text]
+--text sends the batches as FASTQ text (random line ends, headers, '+' lines) through hpgq_batch_submit_text and
+compares the records composed on the device (hpgq_batch_wait_text) as well.
 Prints one line per case and exits non-zero at the first difference."""
 from __future__ import annotations
 
@@ -40,11 +42,94 @@ def rand_batch(rng, n, lmin, lmax, p_n, lower, uniform, hiq):
     return seq, qual, idx
 
 
+def text_case(q, ob, rng, case, seed):
+    """One random batch as FASTQ text: parser + QC + (sometimes) the output records composed on the device."""
+    kind = rng.choice(["short", "short", "mid", "tiny", "long"])
+    lmin, lmax, n = {"short": (int(rng.integers(0, 60)), int(rng.integers(60, 400)), int(rng.integers(1, 30000))),
+                     "mid": (int(rng.integers(100, 640)), int(rng.integers(641, 1100)), int(rng.integers(1, 3000))),
+                     "long": (int(rng.integers(200, 3000)), int(rng.integers(3000, 9000)), int(rng.integers(1, 300))),
+                     "tiny": (0, int(rng.integers(1, 40)), int(rng.integers(1, 300)))}[kind]
+    uniform = bool(rng.random() < 0.3)
+    seq, qual, idx = rand_batch(rng, n, lmin, lmax, float(rng.choice([0.0, 0.01, 0.05])),
+                                float(rng.choice([0.0, 0.0, 0.01])), uniform, False)
+    eol = b"\r\n" if rng.random() < 0.3 else b"\n"
+    final_eol = bool(rng.random() < 0.7)
+    plus_names = bool(rng.random() < 0.3)
+    hl = rng.integers(1, 60, size=n)
+    hb = rng.choice(np.frombuffer(b"abcXYZ019:/_ @+\t#", dtype=np.uint8), size=int(hl.sum()) + 1).tobytes()
+    ho = np.concatenate([[0], np.cumsum(hl)])
+    hdr = lambda i: b"@" + hb[ho[i]:ho[i + 1]]
+    sb, qb = seq.tobytes(), qual.tobytes()
+    parts = []
+    for i in range(n):
+        h = hdr(i)
+        parts.append(h + eol + sb[idx[i]:idx[i + 1]] + eol + (b"+" + h[1:] if plus_names else b"+") + eol + qb[idx[i]:idx[i + 1]] + eol)
+    text = b"".join(parts)
+    if not final_eol:
+        text = text[:-len(eol)]
+    flt = dict(min_read_length=int(rng.integers(0, max(lmax // 2, 1))), min_read_quality=int(rng.integers(0, 30)),
+               max_N=int(rng.integers(0, max(lmax // 10, 2))))
+    edit = dict(left_length=int(rng.integers(0, 40)), min_left_quality=int(rng.integers(10, 38)),
+                right_length=int(rng.integers(0, 40)), min_right_quality=int(rng.integers(10, 38)))
+    mode = rng.choice(["stats_filter", "edit_text", "filter_text"])
+    if mode == "stats_filter":
+        work, parkw = q.WORK_STATS | q.WORK_FILTER, dict(filter=flt)
+    elif mode == "edit_text":
+        work = q.WORK_EDIT | q.WORK_COMPACT | (q.WORK_FILTER if rng.random() < 0.7 else 0)
+        parkw = dict(edit=edit, filter=flt if work & q.WORK_FILTER else None)
+    else:
+        work, parkw = q.WORK_FILTER | q.WORK_COMPACT, dict(filter=flt)
+    par = q.make_params(int(work), **parkw)
+    Lcap = (max(lmax, 1) + 63) // 64 * 64
+    desc = (f"text case {case}: {kind} n={n} L={lmin}-{lmax}{' uniform' if uniform else ''} {mode} eol={eol!r} "
+            f"final_eol={final_eol} plus_names={plus_names} bytes={len(text)}")
+    with q.Ctx(0, max_reads=n + 4, max_bytes=max(int(idx[-1]), 16) + 64, max_read_len=Lcap) as ctx:
+        ctx.set_params(par)
+        info = ctx.submit_text(text, 0)
+        if info.status != 0 or info.n_reads != n:
+            print("FAIL " + desc + f" submit_text status {info.status} reads {info.n_reads} bad record {info.bad_record}")
+            return False
+        res = ctx.wait_text(0) if work & q.WORK_COMPACT else ctx.wait(0)
+        got, lay = ctx.counters(), ctx.layout
+    exp, emask, etrim = ob.process_batch(par, lay, seq, qual, idx)
+    skip = {q.S[k] for k in IGNORE}
+    bad = [int(b) for b in np.nonzero(got != exp)[0] if int(b) not in skip]
+    ok = not bad
+    if ok and work & q.WORK_COMPACT:
+        cp = ob.compact(seq, qual, idx, emask if work & q.WORK_FILTER else None, etrim if work & q.WORK_EDIT else None)
+        oseq, oqual, oidx, osrc = cp["out_seq"].tobytes(), cp["out_qual"].tobytes(), cp["out_idx"], cp["out_src"]
+        rec = lambda a, b: b"".join(hdr(int(osrc[k])) + b"\n" + oseq[oidx[k]:oidx[k + 1]] + b"\n+\n" + oqual[oidx[k]:oidx[k + 1]] + b"\n"
+                                    for k in range(a, b))
+        npass = cp["n_passed"] if work & q.WORK_FILTER else n
+        ok = res["n_passed"] == npass and res["passed_text"] == rec(0, npass) and res["failed_text"] == rec(npass, n)
+    elif ok:
+        ok = np.array_equal(res["mask"], emask)
+    print(("ok   " if ok else "FAIL ") + desc + (f" first bad words {bad[:6]}" if bad else ""), flush=True)
+    if not ok:
+        with open(os.path.join(ROOT, "gpurun_out", f"stress_text_fail_{seed}_{case}.fq"), "wb") as f:
+            f.write(text)
+        print(f"     filter {flt if work & q.WORK_FILTER else None}, edit {edit if work & q.WORK_EDIT else None}")
+    return ok
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--cases", type=int, default=60)
     ap.add_argument("--seed", type=int, default=1)
+    ap.add_argument("--text", action="store_true")
     args = ap.parse_args()
+    if args.text:
+        import __graft_entry__ as g
+        import oracle_binding as ob
+        q = g.load_package().hpgq
+        ob.lib()
+        os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+        rng = np.random.default_rng(1000 + args.seed)
+        for case in range(args.cases):
+            if not text_case(q, ob, rng, case, args.seed):
+                return 1
+        print(f"{args.cases} text cases ok (seed {args.seed})")
+        return 0
     import __graft_entry__ as g
     import oracle_binding as ob
     q = g.load_package().hpgq
@@ -89,8 +174,8 @@ def main():
             parkw, ctxkw = dict(filter=flt, k2=k2, cg_k=ck), dict(kmers=True, k2=k2, cg_k=ck)
         if (work & (q.WORK_KMERS | q.WORK_CHAOS)) and kind == "long":
             n = min(n, 80)
-        seq, qual, idx = rand_batch(rng, n, lmin, lmax, float(rng.choice([0.0, 0.01, 0.05])),
-                                    float(rng.choice([0.0, 0.0, 0.01])), uniform, bool(rng.random() < 0.3))
+        seq, qual, idx = rand_batch(rng, n, lmin, lmax, float(rng.choice([0.0, 0.01, 0.05, 0.5])),
+                                    float(rng.choice([0.0, 0.0, 0.01, 0.3])), uniform, bool(rng.random() < 0.3))
         par = q.make_params(int(work), **parkw)
         Lcap = (max(lmax, 1) + 63) // 64 * 64
         desc = f"case {case}: {kind} n={n} L={lmin}-{lmax}{' uniform' if uniform else ''} {mode} k2={k2} ck={ck}"
