@@ -115,7 +115,7 @@ def test_lowercase_and_foreign_bytes_take_exact_path(q, ob):
 
 
 @pytest.mark.parametrize("grid_cap", [None, 20, 7])
-@pytest.mark.parametrize("lens", [(25, 114), (0, 60), (130, 250)])
+@pytest.mark.parametrize("lens", [(25, 114), (0, 60), (130, 250), (100, 100), (151, 151)])
 def test_foreign_bytes_in_ragged_reads_every_grid(q, ob, lens, grid_cap, monkeypatch):
     """Ragged reads with 1 % lower-case bytes: most warps of the general tiled kernel take the exact path in most
     iterations.  Found by tools/stress_parity.py: with a per-byte if/else chain in that path the warp's cadence
@@ -125,12 +125,14 @@ def test_foreign_bytes_in_ragged_reads_every_grid(q, ob, lens, grid_cap, monkeyp
         monkeypatch.setenv("HPGQ_GRID_CAP", str(grid_cap))
     rng = np.random.default_rng(31)
     seq, qual, idx = rand_batch(rng, 30340, lens[0], lens[1], p_n=0.05, lower=0.01)
-    flt = dict(min_read_length=lens[0] + 11, min_read_quality=0, max_N=max(lens[1] // 20, 1))
+    flt = dict(min_read_length=min(lens[0] + 11, lens[1]), min_read_quality=0, max_N=max(lens[1] // 20, 1))
     for work in (q.WORK_FILTER, q.WORK_STATS | q.WORK_FILTER, q.WORK_STATS):
         par = q.make_params(work, filter=flt if work & q.WORK_FILTER else None)
         got, res, exp, emask, _ = check(q, ob, par, seq, qual, idx, (lens[1] + 63) // 64 * 64)
         if work & q.WORK_FILTER:
             assert res["n_passed"] + res["n_failed"] == 30340 and 0 < res["n_passed"] < 30340
+        if lens[0] == lens[1]:  # the aligned-word loop (device-resident batch stated as uniform) has the same path
+            _device_check(q, ob, par, seq, qual, idx, (lens[1] + 63) // 64 * 64, uniform=True)
     assert got[q.S["SLOW_READS"]] > 0
 
 
