@@ -1,9 +1,10 @@
 #!/usr/bin/env python
 """Randomised parity stress on the GPU box: random batch shapes and option sets through the C ABI, every counter,
 mask, trim record and compacted array compared with the oracle (test infrastructure, like tests/).  Developer tool:
-    python tools/stress_parity.py [--cases 60] [--seed 1] [--text]
+    python tools/stress_parity.py [--cases 60] [--seed 1] [--text | --multi]
 --text sends the batches as FASTQ text (random line ends, headers, '+' lines) through hpgq_batch_submit_text and
-compares the records composed on the device (hpgq_batch_wait_text) as well.
+compares the records composed on the device (hpgq_batch_wait_text) as well.  --multi keeps one context over several
+batches of changing shapes on two slots (host and device-resident submits mixed) and checks the accumulated counters.
 Prints one line per case and exits non-zero at the first difference."""
 from __future__ import annotations
 
@@ -112,12 +113,133 @@ def text_case(q, ob, rng, case, seed):
     return ok
 
 
+def multi_case(q, ob, rng, case):
+    """One context, 3-7 batches of changing shapes over two slots (host and device-resident submits mixed), one option
+    set: accumulated counters and every batch's mask / trim / compacted output."""
+    import ctypes as C
+    nb = int(rng.integers(3, 8))
+    mode = rng.choice(["stats", "stats_filter", "filter_compact", "edit", "all_stats"])
+    Lmax_ctx = int(rng.choice([120, 300, 700, 5000]))
+    flt = dict(min_read_length=int(rng.integers(0, Lmax_ctx // 3)), min_read_quality=int(rng.integers(0, 30)),
+               max_N=int(rng.integers(0, max(Lmax_ctx // 10, 2))))
+    if rng.random() < 0.3:
+        flt.update(max_out_of_quality=int(rng.integers(0, Lmax_ctx)), left_length=int(rng.integers(1, 30)),
+                   min_left_quality=int(rng.integers(5, 30)), right_length=int(rng.integers(1, 30)),
+                   min_right_quality=int(rng.integers(5, 30)))
+    edit = dict(left_length=int(rng.integers(0, 40)), min_left_quality=int(rng.integers(10, 38)),
+                right_length=int(rng.integers(0, 40)), min_right_quality=int(rng.integers(10, 38)))
+    k2, ck = int(rng.integers(2, 12)), int(rng.integers(2, 11))
+    ctxkw, parkw = {}, {}
+    if mode == "stats":
+        work = q.WORK_STATS
+    elif mode == "stats_filter":
+        work, parkw = q.WORK_STATS | q.WORK_FILTER, dict(filter=flt)
+    elif mode == "filter_compact":
+        work, parkw = q.WORK_FILTER | q.WORK_COMPACT, dict(filter=flt)
+    elif mode == "edit":
+        work = q.WORK_EDIT | q.WORK_COMPACT | (q.WORK_FILTER if rng.random() < 0.7 else 0)
+        parkw = dict(edit=edit, filter=flt if work & q.WORK_FILTER else None)
+    else:
+        work = q.WORK_STATS | q.WORK_FILTER | q.WORK_KMERS | q.WORK_CHAOS
+        parkw, ctxkw = dict(filter=flt, k2=k2, cg_k=ck), dict(kmers=True, k2=k2, cg_k=ck)
+    par = q.make_params(int(work), **parkw)
+    Lcap = (Lmax_ctx + 63) // 64 * 64
+    max_reads, max_bytes = 20000, 20000 * min(Lmax_ctx, 400) + 4 * Lmax_ctx
+    shapes = []
+    for b in range(nb):
+        lmax = int(rng.integers(1, Lmax_ctx + 1))
+        lmin = int(rng.integers(0, lmax + 1))
+        uniform = bool(rng.random() < 0.3)
+        n = int(rng.integers(0, max_reads + 1))
+        n = max(min(n, max_bytes // max(lmax, 1) - 1), 0)
+        if work & (q.WORK_KMERS | q.WORK_CHAOS):
+            n = min(n, 3000)
+        shapes.append((n, lmin, lmax, uniform, bool(rng.random() < 0.5)))
+    desc = f"multi case {case}: {mode} Lctx={Lmax_ctx} k2={k2} ck={ck} batches " + " ".join(
+        f"[n={n} L={a}-{b}{'u' if u else ''}{' dev' if d else ''}]" for n, a, b, u, d in shapes)
+    ok, why = True, ""
+    with q.Ctx(0, max_reads=max_reads, max_bytes=max_bytes, max_read_len=Lcap, n_slots=2, **ctxkw) as ctx:
+        ctx.set_params(par)
+        lay = ctx.layout
+        exp = np.zeros(lay.words, dtype=np.uint64)
+        pending = [None, None]
+
+        def retire(slot):
+            nonlocal ok, why
+            p = pending[slot]
+            if p is None:
+                return
+            pending[slot] = None
+            b, dev, seq, qual, idx, emask, etrim = p
+            if dev is not None:
+                ctx.sync(slot)
+                views = q.Result()
+                q._ck(ctx.lib.hpgq_batch_device_views(ctx.h, slot, C.byref(views)), "device_views")
+                n = len(idx) - 1
+                mask = ctx.dev_download(views.mask, n) if n and (work & q.WORK_FILTER) else emask
+                ctx.free_batch(dev)
+                if not np.array_equal(mask, emask):
+                    ok, why = False, f"batch {b}: mask (device views)"
+                return
+            res = ctx.wait(slot)
+            if not np.array_equal(res["mask"], emask):
+                ok, why = False, f"batch {b}: mask differs at {np.nonzero(res['mask'] != emask)[0][:6]}"
+            elif (work & q.WORK_EDIT) and not np.array_equal(res["trim"], etrim):
+                ok, why = False, f"batch {b}: trim"
+            elif work & q.WORK_COMPACT:
+                cp = ob.compact(seq, qual, idx, emask if work & q.WORK_FILTER else None, etrim if work & q.WORK_EDIT else None)
+                for k in ("out_idx", "out_src", "out_seq", "out_qual"):
+                    if not np.array_equal(res[k], cp[k]):
+                        ok, why = False, f"batch {b}: {k}"
+                        break
+
+        for b, (n, lmin, lmax, uniform, dev) in enumerate(shapes):
+            slot = b & 1
+            retire(slot)
+            seq, qual, idx = rand_batch(rng, n, lmin, lmax, float(rng.choice([0.0, 0.01, 0.05])),
+                                        float(rng.choice([0.0, 0.0, 0.01])), uniform, bool(rng.random() < 0.2))
+            exp, emask, etrim = ob.process_batch(par, lay, seq, qual, idx, counters=exp, finalize=False)
+            if dev and n > 0 and not (work & q.WORK_COMPACT):
+                d = ctx.upload_batch(seq, qual, idx, max_len=lmax)
+                uni = uniform and bool(rng.random() < 0.7)
+                ctx.submit_device(d, slot, max_len_hint=None if (uni or rng.random() < 0.5) else 0, uniform=uni)
+                pending[slot] = (b, d, seq, qual, idx, emask, etrim)
+            else:
+                ctx.submit(seq, qual, idx, slot)
+                pending[slot] = (b, None, seq, qual, idx, emask, etrim)
+        retire(0)
+        retire(1)
+        got = ctx.counters()
+    ob.lib().oracle_finalize(C.byref(lay), exp.ctypes.data_as(C.c_void_p))
+    skip = {q.S[k] for k in IGNORE}
+    bad = [int(b) for b in np.nonzero(got != exp)[0] if int(b) not in skip]
+    if bad and ok:
+        names = {v: k for k, v in q.S.items()}
+        ok, why = False, "counters: " + ", ".join(f"{names.get(b, b)} got {int(got[b])} exp {int(exp[b])}" for b in bad[:6])
+    print(("ok   " if ok else "FAIL ") + desc + ("  -- " + why if why else ""), flush=True)
+    if not ok:
+        print(f"     filter {flt if work & q.WORK_FILTER else None}, edit {edit if work & q.WORK_EDIT else None}")
+    return ok
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--cases", type=int, default=60)
     ap.add_argument("--seed", type=int, default=1)
     ap.add_argument("--text", action="store_true")
+    ap.add_argument("--multi", action="store_true")
     args = ap.parse_args()
+    if args.multi:
+        import __graft_entry__ as g
+        import oracle_binding as ob
+        q = g.load_package().hpgq
+        ob.lib()
+        rng = np.random.default_rng(2000 + args.seed)
+        for case in range(args.cases):
+            if not multi_case(q, ob, rng, case):
+                return 1
+        print(f"{args.cases} multi cases ok (seed {args.seed})")
+        return 0
     if args.text:
         import __graft_entry__ as g
         import oracle_binding as ob
