@@ -331,7 +331,10 @@ __global__ void __launch_bounds__(256) hq_qc_regs_kernel(hq_kargs a) {
 }
 
 // ---------------------------------------------------------------- per-position tables, column-owner form
-constexpr int POS_THREADS = 256;
+#ifndef HQ_POS_THREADS
+#define HQ_POS_THREADS 256
+#endif
+constexpr int POS_THREADS = HQ_POS_THREADS;
 constexpr int POS_PER = 8;                       // positions owned by a thread (two 32-bit words)
 constexpr int POS_TILE = POS_THREADS * POS_PER;  // positions per CTA
 constexpr int POS_BATCH = 8;                     // reads in flight per thread (memory-level parallelism)
@@ -353,8 +356,17 @@ __device__ __forceinline__ void load8(const uint8_t *base, uint32_t off, uint32_
 // its eight positions of each read from shared memory.  NS - 1 stages (of POS_RB reads x 2 x 2 KB) are in flight per
 // CTA, so HBM latency is hidden without spending registers on loads.  (One 1-D bulk copy per read and array was
 // measured first: ~0.7 M copies of 2 KB per launch sustain only 1.9 TB/s, the TMA engine is op-rate bound there.)
+// Four CTAs per SM (32 warps): the kernel is bound by latency, not by issue or HBM.  That takes <= 64 registers, so a
+// thread keeps no wide per-position sums: its packed 8-bit / 16-bit lanes go to the global tables every ~240 reads
+// (one reduction per non-zero lane), and a 50 KB ring of 3 stages x 4 reads.  C5 batch on B200: 0.745 ms with 2 CTAs,
+// 8 x 3 ring and 48 wide registers; 0.80 with the direct flush alone; 0.73 / 0.72 with 3 CTAs (4 x 3 / 8 x 2 rings);
+// **0.68** with 4 CTAs and 4 x 3 (6 x 2: 0.69, 3 x 4: 0.72); 5 CTAs at 48 registers (spills): 0.71; 512 threads x 2
+// CTAs: 0.77 (profiles/pos_r2_summary.md).
+#ifndef HQ_POS_CTAS
+#define HQ_POS_CTAS 4
+#endif
 #ifndef HQ_POS_RB
-#define HQ_POS_RB 8   // 8 reads x 3 stages: 1.08 against 1.14 ms per C5 batch with 4 x 4 (profiles/sweep_c5_r2.log)
+#define HQ_POS_RB 4
 #endif
 #ifndef HQ_POS_NS
 #define HQ_POS_NS 3
@@ -403,7 +415,7 @@ __device__ __forceinline__ void lds8(const uint8_t *slot, uint32_t x, uint32_t &
 //         long reads are read once; MODE 2 then takes the reads that FAILED out of the tables again.
 // MODE 2: the reads with mask == 0, subtracted.
 template <int MODE>
-__global__ void __launch_bounds__(POS_THREADS, 2) hq_pos_kernel(hq_kargs a, uint32_t reads_per_slab) {
+__global__ void __launch_bounds__(POS_THREADS, HQ_POS_CTAS) hq_pos_kernel(hq_kargs a, uint32_t reads_per_slab) {
   extern __shared__ __align__(128) uint8_t pos_raw[];
   pos_smem &sm = *reinterpret_cast<pos_smem *>(pos_raw);
   const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
@@ -484,11 +496,6 @@ __global__ void __launch_bounds__(POS_THREADS, 2) hq_pos_kernel(hq_kargs a, uint
     hq_cp_async_arrive_noinc(&sm.full[s]);
   };
 
-  uint32_t acc[6][POS_PER];  // quality sum, A, C, G, T, N per owned position
-#pragma unroll
-  for (int t = 0; t < 6; ++t)
-#pragma unroll
-    for (int i = 0; i < POS_PER; ++i) acc[t][i] = 0u;
   uint32_t pk[5][2] = {{0u, 0u}, {0u, 0u}, {0u, 0u}, {0u, 0u}, {0u, 0u}};  // 8-bit lanes: A C G T N
   uint32_t q16[2][2] = {{0u, 0u}, {0u, 0u}};                               // 16-bit lanes: (byte0, byte2), (byte1, byte3)
   uint32_t nb[3][2] = {{0u, 0u}, {0u, 0u}, {0u, 0u}};  // 4-bit lanes (<= 15 reads): C | G << 4, A | T << 4, N
@@ -506,6 +513,28 @@ __global__ void __launch_bounds__(POS_THREADS, 2) hq_pos_kernel(hq_kargs a, uint
     }
   };
 
+  // 8-bit / 16-bit lanes -> the global tables (one reduction per non-zero lane), instead of 48 wide registers
+  auto flush_wide = [&]() {
+    unsigned long long *Cw = a.ctr;
+    auto put = [&](uint32_t secw, uint32_t pos, uint32_t v) {
+      if (v && pos < a.Lcap) atomicAdd(&Cw[secw + pos], MODE == 2 ? 0ull - (unsigned long long)v : (unsigned long long)v);
+    };
+    const uint32_t secs[5] = {a.o_A, a.o_C, a.o_G, a.o_T, a.o_N};
+#pragma unroll
+    for (int w = 0; w < 2; ++w) {
+#pragma unroll
+      for (int t = 0; t < 5; ++t) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) put(secs[t], p + 4 * w + i, (pk[t][w] >> (8 * i)) & 0xFFu);
+        pk[t][w] = 0u;
+      }
+      put(a.o_accq, p + 4 * w + 0, q16[0][w] & 0xFFFFu);
+      put(a.o_accq, p + 4 * w + 2, q16[0][w] >> 16);
+      put(a.o_accq, p + 4 * w + 1, q16[1][w] & 0xFFFFu);
+      put(a.o_accq, p + 4 * w + 3, q16[1][w] >> 16);
+      q16[0][w] = q16[1][w] = 0u;
+    }
+  };
   if (warp == 0) produce(POS_RB * POS_NS);
   __syncthreads();  // barriers initialised, first descriptors visible
   for (uint32_t j = 0; j + 1 < POS_NS; ++j) issue(j);
@@ -613,44 +642,13 @@ __global__ void __launch_bounds__(POS_THREADS, 2) hq_pos_kernel(hq_kargs a, uint
       fold_nibbles();
       nsince = 0;
     }
-    if (nsince == 0u && since + 15u > 255u) {  // widen before an 8-bit (or 16-bit) lane can overflow
-#pragma unroll
-      for (int w = 0; w < 2; ++w) {
-#pragma unroll
-        for (int t = 0; t < 5; ++t) {
-#pragma unroll
-          for (int i = 0; i < 4; ++i) acc[1 + t][4 * w + i] += (pk[t][w] >> (8 * i)) & 0xFFu;
-          pk[t][w] = 0u;
-        }
-        acc[0][4 * w + 0] += q16[0][w] & 0xFFFFu;
-        acc[0][4 * w + 2] += q16[0][w] >> 16;
-        acc[0][4 * w + 1] += q16[1][w] & 0xFFFFu;
-        acc[0][4 * w + 3] += q16[1][w] >> 16;
-        q16[0][w] = q16[1][w] = 0u;
-      }
+    if (nsince == 0u && since + 15u > 255u) {  // before an 8-bit (or 16-bit) lane can overflow
+      flush_wide();
       since = 0;
     }
   }
   fold_nibbles();
-#pragma unroll
-  for (int w = 0; w < 2; ++w) {
-#pragma unroll
-    for (int t = 0; t < 5; ++t)
-#pragma unroll
-      for (int i = 0; i < 4; ++i) acc[1 + t][4 * w + i] += (pk[t][w] >> (8 * i)) & 0xFFu;
-    acc[0][4 * w + 0] += q16[0][w] & 0xFFFFu;
-    acc[0][4 * w + 2] += q16[0][w] >> 16;
-    acc[0][4 * w + 1] += q16[1][w] & 0xFFFFu;
-    acc[0][4 * w + 3] += q16[1][w] >> 16;
-  }
-  unsigned long long *C = a.ctr;
-  const uint32_t sec[6] = {a.o_accq, a.o_A, a.o_C, a.o_G, a.o_T, a.o_N};
-#pragma unroll
-  for (int t = 0; t < 6; ++t)
-#pragma unroll
-    for (int i = 0; i < POS_PER; ++i)
-      if (acc[t][i] && p + i < a.Lcap)
-        atomicAdd(&C[sec[t] + p + i], MODE == 2 ? 0ull - (unsigned long long)acc[t][i] : (unsigned long long)acc[t][i]);
+  flush_wide();
 }
 
 // Decisions and per-read statistics from the sums hq_pos_kernel<1> has collected (one thread per read); the sums are
@@ -763,10 +761,12 @@ template <int MODE>
 cudaError_t launch_pos_mode(const hq_kargs &a, uint32_t max_len_in_batch, int sm_count, cudaStream_t st, uint64_t *launches) {
   const uint32_t cover = max_len_in_batch < a.Lcap ? max_len_in_batch : a.Lcap;
   const uint32_t tiles = (cover + POS_TILE - 1u) / POS_TILE;
-  // 2 CTAs are resident per SM (100 KB ring each: 3 stages x 8 reads x 2 arrays x 2 080 bytes, <= 128 registers): four waves, the tiles near the longest reads
-  // see few reads and finish early
-  uint32_t slabs = ((uint32_t)sm_count * 8u) / tiles;
-  // a thread widens its packed lanes every 248 reads and keeps u32 sums: any slab size is safe below 2^24 reads
+  // HQ_POS_CTAS CTAs are resident per SM; `waves` grid waves (HPGQ_POS_WAVES, developer knob): the tiles near the
+  // longest reads see few reads and finish early, and every CTA ends with one reduction per non-zero lane
+  const char *wv = getenv("HPGQ_POS_WAVES");
+  const uint32_t waves = wv && atoi(wv) > 0 ? (uint32_t)atoi(wv) : 6u;  // 2: 0.76, 3: 0.70, 4: 0.69, 6: 0.67, 8: 0.69 ms per C5 batch
+  uint32_t slabs = ((uint32_t)sm_count * waves * (uint32_t)HQ_POS_CTAS) / tiles;
+  // a thread empties its packed lanes every ~240 reads: any slab size is safe
   if (slabs > a.n_reads) slabs = a.n_reads;
   if (slabs < 1u) slabs = 1u;
   if (slabs > 65535u) slabs = 65535u;
