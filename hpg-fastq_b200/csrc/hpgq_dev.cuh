@@ -62,6 +62,17 @@ HQ_HDI uint32_t hq_tail_mask(uint32_t p, uint32_t L) {
   const int32_t v = (int32_t)L - (int32_t)p;
   return v >= 4 ? 0xFFFFFFFFu : (v <= 0 ? 0u : ((1u << (8 * v)) - 1u));
 }
+#ifdef __CUDACC__
+// The same mask in five instructions without a branch or select: t = bytes of the word at or past L, clamped to
+// [0, 4]; all-ones shifted right by 8 t with the shift count clamped at 32 (SHF.R.CLAMP).  For the general tiled loop,
+// which recomputes K of these whenever the read length changes -- every iteration on ragged reads, 15 % of its
+// instructions with the form above (profiles/tiled_gen_r2w_summary.md).  Not used by the aligned-word loop: any change
+// to that kernel's set-up code reshuffles ptxas' schedule of its hot loop (509 -> 523 us per 2^23 reads, same box).
+__device__ __forceinline__ uint32_t hq_tail_mask_shf(uint32_t p, uint32_t L) {
+  const int32_t t = min(max((int32_t)(p + 4u - L), 0), 4);
+  return __funnelshift_rc(0xFFFFFFFFu, 0u, 8u * (uint32_t)t);
+}
+#endif
 // 0x01 per byte for positions in [lo, hi)
 HQ_HDI uint32_t hq_range_ones(uint32_t p, uint32_t lo, uint32_t hi) {
   return (hq_tail_mask(p, hi) & ~hq_tail_mask(p, lo)) & 0x01010101u;
