@@ -1108,7 +1108,6 @@ cudaError_t hq_launch_fz(const hq_kargs &a, const hq_compact_bufs &b, uint32_t m
   if (e == cudaSuccess) e = cudaMemsetAsync(z.agg, 0, (size_t)z.n_tiles * sizeof(fz_rec), st);
   if (e == cudaSuccess) e = cudaMemsetAsync(z.incl, 0, (size_t)(2u + ((z.n_tiles + 31u) >> 5) + ((z.n_tiles + 1023u) >> 10)) * sizeof(fz_rec), st);
   if (e != cudaSuccess) return e;
-  const uint32_t smem = (((uint32_t)sizeof(fz_hdr) + 15u) & ~15u) + ct_rmap_bytes(z.cap) + 2u * z.cap;
   const uint32_t span = max_len + 15u;
   int G = span <= 4u * RG_LB ? 4 : span <= 8u * RG_LB ? 8 : span <= 16u * RG_LB ? 16 : 32;
   const bool ooq = (a.work & HPGQ_WORK_FILTER) != 0 && a.max_ooq < 32 * RG_LB;
@@ -1117,6 +1116,11 @@ cudaError_t hq_launch_fz(const hq_kargs &a, const hq_compact_bufs &b, uint32_t m
   const bool windows = (a.work & HPGQ_WORK_FILTER) != 0 && (a.f_ll > 0 || a.f_rl > 0);
   bool fast = !ooq && !windows && a.e_ll <= 255 && a.e_rl <= 255 && max_len <= 20u * 32u - 3u && !getenv("HPGQ_FZ_SLOW");
   if (fast) G = max_len <= 77u ? 4 : max_len <= 157u ? 8 : max_len <= 317u ? 16 : 32;
+  // fz_decide_fast loads whole frames (4 K G + 4 bytes from a read's first word) whatever the read's length: the last
+  // reads of a tile that fills its staged span reach up to a frame past the quality array, the last thing in the CTA's
+  // shared memory (found by tools/stress_parity.py: 60 reads x 363 bp per tile, illegal address).  One frame of slack.
+  const uint32_t smem = (((uint32_t)sizeof(fz_hdr) + 15u) & ~15u) + ct_rmap_bytes(z.cap) + 2u * z.cap +
+                        (fast ? 4u * 5u * (uint32_t)G + 16u : 0u);
   if (a.n_reads) {
 #define HQ_FZ(KK, GG, OO, FF)                                                                                     \
   do {                                                                                                           \

@@ -590,6 +590,23 @@ def test_one_pass_word_frame_decisions_on_ragged_reads(q, ob, lmax, monkeypatch)
             assert np.array_equal(res[k], cp[k]), k
 
 
+@pytest.mark.parametrize("L", [363, 630, 150, 77])
+def test_one_pass_word_frame_on_full_tiles(q, ob, L):
+    """Tiles of the one-pass kernel that fill their staged span (uniform reads, 22 000 / L per tile): the word-frame
+    decision loads a whole frame per read, for the tile's last reads beyond the staged bytes -- past the CTA's shared
+    memory before the launcher left a frame of slack (illegal address at 60 x 363 bp, tools/stress_parity.py)."""
+    rng = np.random.default_rng(L)
+    seq, qual, idx = rand_batch(rng, 18000, L, L, p_n=0.03)
+    edit = dict(left_length=4, min_left_quality=19, right_length=6, min_right_quality=20)
+    for work, flt in ((q.WORK_EDIT | q.WORK_COMPACT, None),
+                      (q.WORK_EDIT | q.WORK_FILTER | q.WORK_COMPACT, dict(min_read_length=L - 5, min_read_quality=22, max_N=L // 25))):
+        par = q.make_params(work, edit=edit, filter=flt, kernel_variant=2)
+        _, res, _, emask, etrim = check(q, ob, par, seq, qual, idx, (L + 63) // 64 * 64)
+        cp = ob.compact(seq, qual, idx, emask if flt else None, etrim)
+        for k in ("out_idx", "out_src", "out_seq", "out_qual"):
+            assert np.array_equal(res[k], cp[k]), k
+
+
 @pytest.mark.parametrize("k2,ck", [(11, 10), (7, 7), (9, 3), (3, 5), (13, 12)])
 def test_kmers_and_chaos_game_single_reduction_path(q, ob, k2, ck, monkeypatch):
     """k-mers + chaos game without a filter: one packed reduction per base, split into K2 / CG_SEQ / CG_Q afterwards

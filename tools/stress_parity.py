@@ -298,9 +298,15 @@ def main():
             n = min(n, 80)
         seq, qual, idx = rand_batch(rng, n, lmin, lmax, float(rng.choice([0.0, 0.01, 0.05, 0.5])),
                                     float(rng.choice([0.0, 0.0, 0.01, 0.3])), uniform, bool(rng.random() < 0.3))
+        if (work & q.WORK_COMPACT) and rng.random() < 0.4:
+            parkw = dict(parkw, kernel_variant=2)  # decisions + compaction in one pass (hq_fz_kernel) where it applies
+            mode += "/one_pass"
         par = q.make_params(int(work), **parkw)
         Lcap = (max(lmax, 1) + 63) // 64 * 64
         desc = f"case {case}: {kind} n={n} L={lmin}-{lmax}{' uniform' if uniform else ''} {mode} k2={k2} ck={ck}"
+        if os.environ.get("STRESS_TRACE"):
+            print("run  " + desc + f" filter {flt} edit {edit}", flush=True)
+            np.savez(os.path.join(ROOT, "gpurun_out", "stress_last.npz"), seq=seq, qual=qual, idx=idx)
         with q.Ctx(0, max_reads=max(n, 1), max_bytes=max(int(idx[-1]), 16), max_read_len=Lcap, **ctxkw) as ctx:
             ctx.set_params(par)
             ctx.submit(seq, qual, idx, 0)
@@ -323,7 +329,7 @@ def main():
                   f"filter {flt if work & q.WORK_FILTER else None}, edit {edit if work & q.WORK_EDIT else None}")
             for env in ({"HPGQ_NO_UNI": "1"}, {"HPGQ_NO_POSFUSE": "1"}, {"VARIANT": "1"}):
                 os.environ.update({k: v for k, v in env.items() if k != "VARIANT"})
-                par2 = q.make_params(int(work), kernel_variant=1 if "VARIANT" in env else 0, **parkw)
+                par2 = q.make_params(int(work), **dict(parkw, kernel_variant=1 if "VARIANT" in env else 0))
                 with q.Ctx(0, max_reads=max(n, 1), max_bytes=max(int(idx[-1]), 16), max_read_len=Lcap, **ctxkw) as ctx:
                     ctx.set_params(par2)
                     ctx.submit(seq, qual, idx, 0)
