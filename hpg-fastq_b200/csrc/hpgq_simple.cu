@@ -612,16 +612,19 @@ __global__ void __launch_bounds__(K5_THREADS, 1) hq_k5pos_kernel(hq_kargs a, uin
       if (L > a.Lcap || L < p0 + 5u || (use_mask && !a.mask[r])) L = 0u;
     }
   };
-  // stage: read i of the group <- lanes 0..K5_SW-1 copy consecutive aligned words of its slice (asynchronously)
+  // stage: two reads of the group per instruction -- lanes 0..15 copy consecutive aligned words of the slice of read i,
+  // lanes 16..31 those of read i + 1 (K5_SW <= 16 words per read), asynchronously
+  static_assert(K5_SW <= 16, "a half warp stages one read");
   auto stage = [&](uint32_t *buf, uint32_t o, uint32_t L) {
+    const uint32_t half = lane >> 4, l16 = lane & 15u;
 #pragma unroll 8
-    for (int i = 0; i < 32; ++i) {
-      const uint32_t oi = __shfl_sync(0xFFFFFFFFu, o, i), Li = __shfl_sync(0xFFFFFFFFu, L, i);
-      if (Li == 0u) continue;  // warp-uniform
-      const uint32_t first = oi + p0, wa = (first & ~3u) + 4u * lane;
+    for (int i = 0; i < 32; i += 2) {
+      const uint32_t src = (uint32_t)i + half;
+      const uint32_t oi = __shfl_sync(0xFFFFFFFFu, o, src), Li = __shfl_sync(0xFFFFFFFFu, L, src);
+      const uint32_t first = oi + p0, wa = (first & ~3u) + 4u * l16;
       const uint32_t last = oi + min(Li, p0 + (uint32_t)K5_W + 4u);  // one past the last byte needed
-      if (lane < (uint32_t)K5_SW && wa < last)
-        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(hq_smem_u32(buf + i * K5_STRIDE + lane)), "l"(a.seq + wa) : "memory");
+      if (Li != 0u && l16 < (uint32_t)K5_SW && wa < last)
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(hq_smem_u32(buf + src * K5_STRIDE + l16)), "l"(a.seq + wa) : "memory");
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
   };
