@@ -683,10 +683,13 @@ __device__ __forceinline__ void fz_len_update(const hq_kargs &a, fz_len_consts<K
 #pragma unroll
   for (int k = 0; k < K; ++k) {
     const uint32_t p = 4u * ((uint32_t)k * G + lig);
-    c.m[k] = hq_tail_mask(p, L);
+    // three clamp + funnel-shift masks per word (hq_tail_mask_shf) instead of five compare / select ones: this block
+    // runs twice per short read of an otherwise uniform batch, for the whole warp, and was 12 % of the decision
+    // kernel's instructions on C3 (2 % short reads; capture dec_r2x)
+    c.m[k] = hq_tail_mask_shf(p, L);
     c.m01[k] = c.m[k] & 0x01010101u;
-    c.ml[k] = hq_range_ones(p, 0u, c.wl);
-    c.mr[k] = hq_range_ones(p, L - c.wr, L);
+    c.ml[k] = hq_tail_mask_shf(p, c.wl) & 0x01010101u;            // positions [0, wl)
+    c.mr[k] = c.m01[k] & ~hq_tail_mask_shf(p, L - c.wr);          // positions [L - wr, L)
   }
 }
 template <int K, int G>
