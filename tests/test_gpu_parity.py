@@ -452,6 +452,20 @@ def test_in_loop_flush_every_geometry(q, ob, L, n, no_uni):
             _device_check(q, ob, par, seq, qual, idx, 640)
 
 
+@pytest.mark.parametrize("no_uni", [None, 1])
+def test_quality_sum_cell_carries_past_32_bits(q, ob, no_uni):
+    """One CTA (HPGQ_GRID_CAP=1) sees 600 000 reads of 150 bp: its sum of quality bytes of that length passes 2^32, so
+    the block-private cell's low word wraps and the carry of the two-word shared-memory add is exercised (a launch of
+    more than ~110 M reads on all 148 SMs gets there too).  Whole counter block against the oracle."""
+    n = 600_000
+    seq, qual, idx = q.synth_host(q.synth_cfg(150), 0, n)
+    assert int(qual.astype(np.uint64).sum()) > (1 << 32)
+    par = q.make_params(q.WORK_STATS | q.WORK_FILTER, filter=dict(min_read_length=50, min_read_quality=2, max_N=150))
+    with _env(HPGQ_NO_UNI=no_uni, HPGQ_GRID_CAP=1):
+        got = _device_check(q, ob, par, seq, qual, idx, 192, uniform=True)
+    assert int(got[q.S["NUM_PASSED"]]) == n  # every read is in the sum
+
+
 @pytest.mark.parametrize("L", [7, 36, 75, 96, 97, 100, 101, 106, 111, 112, 113, 149, 150, 151, 250, 251, 253, 300, 301, 302, 600, 637, 640])
 def test_uniform_kernel_lengths_and_phases(q, ob, L):
     """Uniform-length kernel over the geometries' length range, odd lengths (where the group count does not keep the
